@@ -1,0 +1,141 @@
+/*
+ * nbody_b200.h -- C ABI of the B200-native N-body hot path (libnbody_b200.so).
+ *
+ * Drop-in boundary for the ONE data-parallel path of sanonesan/parallel_comp_labs:
+ * the all-pairs clamped-softening acceleration evaluated at every stage of the
+ * explicit Runge-Kutta N-body integrator (lab_4_N_body_MPI / lab_5_N_body_CUDA).
+ * Plain pointers and sizes only; no C++/torch types; never throws; no CPU fallback
+ * (nbody_create fails without an sm_100 device).
+ *
+ * Each entry point cites the reference interface it replaces (file:line relative to
+ * the reference repository root).  One context == one GPU == one "rank"
+ * (the MPI rank of lab_4).  A context is not thread-safe; distinct contexts may be
+ * driven from distinct threads or processes.
+ *
+ * Body layouts accepted at the boundary
+ *   AoS  Body<T> {T m; T r[3]; T v[3];}            lab_4 .../struct_Body.hpp:5-10
+ *   SoA  T m[n]; T3 r[n]; T3 v[n] (T3 = float4/double4, .w ignored)
+ *                                                   lab_5 N_body.cu:19-27,40-62
+ * T is double (precision 64) or float (precision 32).
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nbody_ctx nbody_ctx;
+
+enum { NBODY_OK = 0, NBODY_ERR_ARG = 1, NBODY_ERR_CUDA = 2, NBODY_ERR_NCCL = 3,
+	   NBODY_ERR_NO_DEVICE = 4, NBODY_ERR_STATE = 5 };
+
+/* Integrator schemes.  2 = explicit midpoint, the reference's only scheme
+ * (lab_4 .../schemes/ode_RK2_MPI.hpp:72-100, lab_5 N_body.cu:299-316);
+ * 4 = classical RK4 over the same RHS (BASELINE.json's metric; not in the reference). */
+enum { NBODY_RK2 = 2, NBODY_RK4 = 4 };
+
+#define NBODY_NCCL_UID_BYTES 128
+
+typedef struct nbody_timing {
+	double last_call_ms;		 /* CUDA-event time of the last nbody_step / nbody_rhs call */
+	double force_ms;			 /* summed CUDA-event time of force-kernel launches in that call
+									(only when option "time_kernels" is 1; else 0) */
+	uint64_t force_launches;	 /* force-kernel launches in that call */
+	uint64_t total_launches;	 /* all kernel launches of this library since create */
+	uint64_t interactions;		 /* body-body interactions evaluated in that call, this rank */
+	uint64_t steps_done;		 /* integrator steps since the last upload */
+} nbody_timing;
+
+/* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
+ * distributes the bytes; replaces MPI_Init's rendezvous, lab_4 N_body.cpp:67). */
+int nbody_nccl_unique_id(void* out);
+
+/* Create the context of rank `rank` of `world` on CUDA device `device`.
+ * Replaces Solver_N_body<T>::solve_parallel_MPI's setup (rank/size query, block
+ * partition, datatype creation: lab_4 .../class_Solver_N_body.hpp:93-179) and
+ * ode_RK2_CUDA's allocation block (lab_5 N_body.cu:257-288).
+ * n = number of bodies (every rank holds all n positions and masses, as every MPI
+ * rank of lab_4 holds the whole array); precision = 64 or 32; world > n is an error
+ * (the reference throws, class_Solver_N_body.hpp:115-117).  nccl_uid may be NULL
+ * when world == 1.  On failure *out is NULL and the message is available through
+ * nbody_last_error(NULL). */
+int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank, int world,
+				 const void* nccl_uid);
+void nbody_destroy(nbody_ctx* ctx);
+
+/* G and eps captured by the RHS lambda (lab_4 .../struct_ode_system.hpp:34-36,53;
+ * lab_5 N_body.cu:22,30).  Defaults 6.67e-11 and 1e-6. */
+int nbody_set_params(nbody_ctx* ctx, double G, double eps);
+
+/* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
+ * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (0/1). */
+int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
+
+/* Rows [begin,end) this rank owns (lab_4's offsets[id], counts[id],
+ * class_Solver_N_body.hpp:119-130; here equal-sized padded blocks). */
+int nbody_owned_range(const nbody_ctx* ctx, size_t* begin, size_t* end);
+
+/* Upload the whole state.  AoS: n x Body<T> = sys.traj_init
+ * (lab_4 .../schemes/ode_RK2_MPI.hpp:55-56).  SoA: lab_5's m, r, v host vectors
+ * (N_body.cu:279-288).  Host pointers are borrowed for the call only. */
+int nbody_upload_aos(nbody_ctx* ctx, const void* bodies);
+int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* v4);
+
+/* Test hook == sys.N_body_func(traj, diff, begin, end) with [begin,end) = owned rows
+ * (lab_4 .../struct_ode_system.hpp:27-30,53-76; lab_5 calc_acceleration N_body.cu:134-195).
+ * Writes diff[i].v (acceleration, 3 x T per row) for owned rows into acc_host[3*i..],
+ * i global; rows not owned are left untouched.  Synchronous. */
+int nbody_rhs(nbody_ctx* ctx, void* acc_host);
+
+/* Advance n_steps steps of size tau with the given scheme; everything stays on the
+ * device.  Replaces the body of the time loop (lab_4 ode_RK2_MPI.hpp:72-92, lab_5
+ * N_body.cu:299-316).  Loop control stays with the caller.
+ * Asynchronous: returns once the work is enqueued; nbody_sync waits.  Collective:
+ * all ranks of the world must call it with the same arguments. */
+int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps);
+int nbody_sync(nbody_ctx* ctx);
+
+/* Asynchronous position snapshot (replaces the per-step cudaMemcpyAsync D2H +
+ * write_bodies_coords of lab_5 N_body.cu:352-367 and rank 0's row write of lab_4
+ * ode_RK2_MPI.hpp:94-96).  Enqueues a device-side pack of all n positions (3 x T per
+ * body) and a copy into a pinned ring slot; returns a ticket.  nbody_snapshot_wait
+ * blocks until that copy has landed and returns the pinned pointer, valid until
+ * nbody_snapshot_release.  The ring has NBODY_SNAPSHOT_SLOTS slots; asking for a
+ * snapshot while all are held is NBODY_ERR_STATE. */
+#define NBODY_SNAPSHOT_SLOTS 4
+int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket);
+int nbody_snapshot_wait(nbody_ctx* ctx, uint64_t ticket, const void** r_host);
+int nbody_snapshot_release(nbody_ctx* ctx, uint64_t ticket);
+
+/* Whole state back as n x Body<T> (superset of the reference, whose final state is
+ * only visible through the CSV; needed for parity on velocities).  Collective when
+ * world > 1 (velocities are owner-local and are gathered here). */
+int nbody_download_aos(nbody_ctx* ctx, void* bodies);
+
+/* Kinetic and potential energy of the current state, potential consistent with the
+ * clamp force.  Not in the reference.  Collective when world > 1. */
+int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential);
+
+int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out);
+
+/* Pinned host memory for callers that want zero-staging transfers. */
+void* nbody_host_alloc(size_t bytes);
+void nbody_host_free(void* p);
+
+/* Sustained FMA-pipe peak of this device in TFLOP/s (2 flops per FMA), measured by a
+ * register-resident dependent-chain microbenchmark of `ms_target` milliseconds:
+ * the roofline denominator for the force kernel (MEASURED_PEAKS.json has no FP64/FP32
+ * vector figure).  precision = 64 or 32. */
+int nbody_measure_fma_peak(int device, int precision, double ms_target, double* tflops);
+
+const char* nbody_last_error(const nbody_ctx* ctx);
+const char* nbody_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

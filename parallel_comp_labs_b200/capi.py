@@ -1,0 +1,236 @@
+"""ctypes binding of the C ABI (include/nbody_b200.h -> libnbody_b200.so).
+
+This is the only way Python reaches the device: there is no Python/CPU implementation
+of the path behind it.  Importing works anywhere (the "does the library load and export
+every symbol" check runs without a GPU); creating a context without an sm_100 device
+raises :class:`NBodyError`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libnbody_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(PKG_DIR), "include", "nbody_b200.h")
+
+NBODY_RK2, NBODY_RK4 = 2, 4
+NCCL_UID_BYTES = 128
+SNAPSHOT_SLOTS = 4
+
+
+class NBodyError(RuntimeError):
+    pass
+
+
+class Timing(C.Structure):
+    _fields_ = [("last_call_ms", C.c_double), ("force_ms", C.c_double),
+                ("force_launches", C.c_uint64), ("total_launches", C.c_uint64),
+                ("interactions", C.c_uint64), ("steps_done", C.c_uint64)]
+
+
+def build_library(quiet: bool = True) -> None:
+    subprocess.run(["make", "-C", os.path.join(PKG_DIR, "csrc")], check=True,
+                   stdout=subprocess.DEVNULL if quiet else None)
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libnbody_b200.so (fails loudly if it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NBodyError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                         f"g.build()'` (or make -C parallel_comp_labs_b200/csrc). "
+                         f"There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, sz = C.c_void_p, C.c_size_t
+    L.nbody_version.restype = C.c_char_p
+    L.nbody_last_error.restype = C.c_char_p
+    L.nbody_last_error.argtypes = [vp]
+    L.nbody_nccl_unique_id.argtypes = [vp]
+    L.nbody_create.argtypes = [C.POINTER(vp), sz, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    L.nbody_destroy.argtypes = [vp]
+    L.nbody_destroy.restype = None
+    L.nbody_set_params.argtypes = [vp, C.c_double, C.c_double]
+    L.nbody_set_option.argtypes = [vp, C.c_char_p, C.c_long]
+    L.nbody_owned_range.argtypes = [vp, C.POINTER(sz), C.POINTER(sz)]
+    L.nbody_upload_aos.argtypes = [vp, vp]
+    L.nbody_upload_soa.argtypes = [vp, vp, vp, vp]
+    L.nbody_rhs.argtypes = [vp, vp]
+    L.nbody_step.argtypes = [vp, C.c_int, C.c_double, C.c_long]
+    L.nbody_sync.argtypes = [vp]
+    L.nbody_snapshot_async.argtypes = [vp, C.POINTER(C.c_uint64)]
+    L.nbody_snapshot_wait.argtypes = [vp, C.c_uint64, C.POINTER(vp)]
+    L.nbody_snapshot_release.argtypes = [vp, C.c_uint64]
+    L.nbody_download_aos.argtypes = [vp, vp]
+    L.nbody_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.nbody_get_timing.argtypes = [vp, C.POINTER(Timing)]
+    L.nbody_host_alloc.restype = vp
+    L.nbody_host_alloc.argtypes = [sz]
+    L.nbody_host_free.argtypes = [vp]
+    L.nbody_host_free.restype = None
+    L.nbody_measure_fma_peak.argtypes = [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+    _lib = L
+    return L
+
+
+def declared_symbols() -> list[str]:
+    """Every function name include/nbody_b200.h declares."""
+    import re
+    txt = open(HEADER_PATH).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(nbody_[a-z0-9_]+)\s*\(", txt)))
+
+
+def nccl_unique_id() -> bytes:
+    buf = C.create_string_buffer(NCCL_UID_BYTES)
+    rc = lib().nbody_nccl_unique_id(buf)
+    if rc:
+        raise NBodyError(lib().nbody_last_error(None).decode())
+    return buf.raw
+
+
+def measure_fma_peak(precision: int = 64, ms_target: float = 200.0, device: int = 0) -> float:
+    out = C.c_double()
+    rc = lib().nbody_measure_fma_peak(device, precision, ms_target, C.byref(out))
+    if rc:
+        raise NBodyError(lib().nbody_last_error(None).decode())
+    return out.value
+
+
+class PinnedArray:
+    """numpy view over cudaHostAlloc memory (nbody_host_alloc)."""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = lib().nbody_host_alloc(self.nbytes)
+        if not self.ptr:
+            raise NBodyError("nbody_host_alloc failed")
+        buf = (C.c_char * self.nbytes).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().nbody_host_free(self.ptr)
+            self.ptr = None
+
+
+class Context:
+    """One GPU / one rank.  Thin RAII wrapper; every method is one C-ABI call."""
+
+    def __init__(self, n: int, precision: int = 64, device: int = 0, rank: int = 0,
+                 world: int = 1, nccl_uid: bytes | None = None):
+        self.L = lib()
+        self.n, self.precision = int(n), int(precision)
+        self.dtype = np.float64 if precision == 64 else np.float32
+        self.rank, self.world = rank, world
+        h = C.c_void_p()
+        uid = C.create_string_buffer(nccl_uid, NCCL_UID_BYTES) if nccl_uid else None
+        rc = self.L.nbody_create(C.byref(h), n, precision, device, rank, world, uid)
+        if rc:
+            raise NBodyError(self.L.nbody_last_error(None).decode())
+        self.h = h
+
+    def _ck(self, rc):
+        if rc:
+            raise NBodyError(self.L.nbody_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.nbody_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_params(self, G=6.67e-11, eps=1e-6):
+        self._ck(self.L.nbody_set_params(self.h, G, eps))
+
+    def set_option(self, name: str, value: int):
+        self._ck(self.L.nbody_set_option(self.h, name.encode(), value))
+
+    def owned_range(self):
+        b, e = C.c_size_t(), C.c_size_t()
+        self._ck(self.L.nbody_owned_range(self.h, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def upload_aos(self, bodies):
+        b = np.ascontiguousarray(bodies, dtype=self.dtype)
+        assert b.shape == (self.n, 7), b.shape
+        self._ck(self.L.nbody_upload_aos(self.h, b.ctypes.data))
+
+    def upload_soa(self, m, r4, v4):
+        m = np.ascontiguousarray(m, dtype=self.dtype)
+        r4 = np.ascontiguousarray(r4, dtype=self.dtype)
+        v4 = np.ascontiguousarray(v4, dtype=self.dtype)
+        assert m.shape == (self.n,) and r4.shape == (self.n, 4) and v4.shape == (self.n, 4)
+        self._ck(self.L.nbody_upload_soa(self.h, m.ctypes.data, r4.ctypes.data, v4.ctypes.data))
+
+    def rhs(self):
+        """Accelerations (n,3); rows outside owned_range() are NaN."""
+        out = np.full((self.n, 3), np.nan, dtype=self.dtype)
+        self._ck(self.L.nbody_rhs(self.h, out.ctypes.data))
+        return out
+
+    def step(self, scheme: int, tau: float, n_steps: int = 1, sync: bool = False):
+        self._ck(self.L.nbody_step(self.h, scheme, tau, n_steps))
+        if sync:
+            self.sync()
+
+    def sync(self):
+        self._ck(self.L.nbody_sync(self.h))
+
+    def snapshot_async(self) -> int:
+        t = C.c_uint64()
+        self._ck(self.L.nbody_snapshot_async(self.h, C.byref(t)))
+        return t.value
+
+    def snapshot_wait(self, ticket: int, copy: bool = True):
+        p = C.c_void_p()
+        self._ck(self.L.nbody_snapshot_wait(self.h, ticket, C.byref(p)))
+        nbytes = self.n * 3 * np.dtype(self.dtype).itemsize
+        a = np.frombuffer((C.c_char * nbytes).from_address(p.value), dtype=self.dtype)
+        a = a.reshape(self.n, 3)
+        return a.copy() if copy else a
+
+    def snapshot_release(self, ticket: int):
+        self._ck(self.L.nbody_snapshot_release(self.h, ticket))
+
+    def snapshot(self):
+        t = self.snapshot_async()
+        a = self.snapshot_wait(t)
+        self.snapshot_release(t)
+        return a
+
+    def download_aos(self, out=None):
+        if out is None:
+            out = np.empty((self.n, 7), dtype=self.dtype)
+        self._ck(self.L.nbody_download_aos(self.h, out.ctypes.data))
+        return out
+
+    def energy(self):
+        k, u = C.c_double(), C.c_double()
+        self._ck(self.L.nbody_energy(self.h, C.byref(k), C.byref(u)))
+        return k.value, u.value
+
+    def timing(self) -> Timing:
+        t = Timing()
+        self._ck(self.L.nbody_get_timing(self.h, C.byref(t)))
+        return t

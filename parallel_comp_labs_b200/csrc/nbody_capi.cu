@@ -1,0 +1,896 @@
+// nbody_capi.cu -- the C ABI declared in include/nbody_b200.h (libnbody_b200.so).
+//
+// One context == one GPU == one rank.  Streams: `sc` compute, `sm` comm (NCCL
+// all-gather of the stage positions, overlapped with the local-tile force launch),
+// `sx` snapshot copies.  NCCL is bound at run time with dlopen so that the single-GPU
+// path has no NCCL dependency and a host process that already carries an NCCL (torch)
+// shares it.  There is NO CPU path in this file: every entry point that computes
+// launches sm_100a kernels or fails.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/nbody_b200.h"
+#include "force_kernels.cuh"
+#include "stage_kernels.cuh"
+
+using namespace nbody;
+
+// ------------------------------------------------------------------ NCCL (dlopen)
+namespace {
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+enum { NCCL_INT8 = 0, NCCL_DOUBLE = 8, NCCL_SUM = 0 };
+struct NcclApi {
+	void* lib = nullptr;
+	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+	ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+	ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+	const char* (*GetErrorString)(ncclResult_t) = nullptr;
+	std::string err;
+	bool load() {
+		if (lib) return true;
+		const char* env = getenv("NBODY_NCCL_LIB");
+		const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+		for (const char* nm : names) {
+			if (!nm) continue;
+			lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+			if (lib) break;
+		}
+		if (!lib) {
+			err = std::string("cannot dlopen NCCL: ") + dlerror();
+			return false;
+		}
+#define NB_SYM(f) *(void**)(&f) = dlsym(lib, "nccl" #f); if (!f) { err = "missing nccl" #f; lib = nullptr; return false; }
+		NB_SYM(GetUniqueId) NB_SYM(CommInitRank) NB_SYM(CommDestroy) NB_SYM(AllGather)
+		NB_SYM(AllReduce) NB_SYM(GetErrorString)
+#undef NB_SYM
+		return true;
+	}
+};
+NcclApi g_nccl;
+thread_local std::string g_err;
+
+struct Variant {
+	int threads, ipt;  // i-bodies per thread
+	size_t smem;
+	const void* fn;
+	void (*launch)(dim3, cudaStream_t, size_t, const ForceParams&, double eps2);
+	const char* name;
+};
+
+template <typename T> Clamp<T> make_clamp(double eps2);
+template <> Clamp<double> make_clamp<double>(double eps2) {
+	Clamp<double> c;
+	memcpy(&c.eps2_bits, &eps2, 8);
+	c.thresh = (int)(c.eps2_bits >> 32);
+	return c;
+}
+template <> Clamp<float> make_clamp<float>(double eps2) {
+	Clamp<float> c;
+	c.eps2 = (float)eps2;
+	memcpy(&c.thresh, &c.eps2, 4);
+	return c;
+}
+
+template <typename T, int TH, int I, int ST, int MB, int JU, int UN, int ORD>
+void launch_force(dim3 grid, cudaStream_t s, size_t smem, const ForceParams& p, double eps2) {
+	force_kernel<T, TH, I, ST, MB, JU, UN, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
+}
+#define NB_VARIANT(T, TH, I, ST, MB, JU, UN, ORD)                                             \
+	Variant { TH, I, force_smem_bytes<T, ST>(),                                                \
+			  (const void*)force_kernel<T, TH, I, ST, MB, JU, UN, ORD>,                         \
+			  launch_force<T, TH, I, ST, MB, JU, UN, ORD>,                                      \
+			  #T "/t" #TH "/i" #I "/s" #ST "/b" #MB "/ju" #JU "/u" #UN "/o" #ORD }
+
+// {threads, i-bodies per thread, ring stages, min CTAs/SM, (unused), j unroll,
+//  correction order of the inverse cube (2 = full double accuracy)}
+const Variant g_var64[] = {
+	NB_VARIANT(double, 128, 2, 3, 6, 1, 8, 2),
+	NB_VARIANT(double, 128, 4, 3, 4, 1, 8, 2),
+	NB_VARIANT(double, 128, 2, 3, 6, 1, 16, 2),
+	NB_VARIANT(double, 128, 2, 3, 8, 1, 8, 2),
+	NB_VARIANT(double, 256, 2, 3, 3, 1, 8, 2),
+	NB_VARIANT(double, 64, 2, 3, 12, 1, 8, 2),
+	NB_VARIANT(double, 128, 1, 3, 8, 1, 16, 2),
+	NB_VARIANT(double, 128, 4, 3, 3, 1, 4, 2),
+	NB_VARIANT(double, 128, 2, 3, 6, 1, 8, 1),
+	NB_VARIANT(double, 128, 4, 3, 4, 1, 4, 1),
+};
+const Variant g_var32[] = {
+	NB_VARIANT(float, 128, 4, 3, 4, 1, 4, 2),
+	NB_VARIANT(float, 128, 8, 3, 4, 1, 4, 2),
+	NB_VARIANT(float, 256, 4, 3, 2, 1, 4, 2),
+	NB_VARIANT(float, 128, 2, 3, 8, 1, 8, 2),
+	NB_VARIANT(float, 256, 8, 3, 2, 1, 2, 2),
+	NB_VARIANT(float, 128, 16, 3, 2, 1, 2, 2),
+};
+constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
+constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
+constexpr unsigned PAD_UNIT = 2048;	 // multiple of every variant's THREADS*I and of TJ
+constexpr unsigned MAX_SLICES = 64;
+}  // namespace
+
+struct nbody_ctx {
+	size_t n = 0;
+	int prec = 64, device = 0, rank = 0, world = 1;
+	unsigned n_pad = 0, own_pad = 0, own0 = 0, own_real = 0;
+	double G = 6.67e-11, eps = 1e-6;
+	size_t esz = 8;	 // sizeof(T)
+	void *Y = nullptr, *P = nullptr, *vel_n = nullptr, *vel_s = nullptr, *acc_r = nullptr,
+		 *acc_v = nullptr, *apart = nullptr, *rhs_out = nullptr, *vel_all = nullptr,
+		 *d_aos = nullptr;
+	unsigned apart_slices = 0;
+	double* d_energy = nullptr;
+	unsigned* d_counters = nullptr;	 // work-unit ticket counters (one per force launch of a stage)
+	void* snap_dev[NBODY_SNAPSHOT_SLOTS] = {};
+	void* snap_host[NBODY_SNAPSHOT_SLOTS] = {};
+	cudaEvent_t snap_ev[NBODY_SNAPSHOT_SLOTS] = {};
+	int snap_state[NBODY_SNAPSHOT_SLOTS] = {};	// 0 free, 1 in flight / held
+	uint64_t snap_ticket[NBODY_SNAPSHOT_SLOTS] = {};
+	uint64_t next_ticket = 1;
+	cudaStream_t sc = nullptr, sm = nullptr, sx = nullptr;
+	cudaEvent_t e_k2 = nullptr, e_g = nullptr, e_snap = nullptr, ev_start = nullptr,
+				ev_stop = nullptr;
+	std::vector<cudaEvent_t> kev;  // pairs around force launches (time_kernels)
+	size_t kev_used = 0;
+	ncclComm_t comm = nullptr;
+	bool y_gathered = true;
+	bool uploaded = false;
+	long opt_time_kernels = 0, opt_slices = 0, opt_variant = -1, opt_use_graph = 0;
+	int n_sm = 148;
+	nbody_timing tm = {};
+	bool timing_pending = false;
+	std::string err;
+	// cached CUDA graph of one step
+	cudaGraphExec_t graph = nullptr;
+	int graph_scheme = 0;
+	double graph_tau = 0;
+};
+
+namespace {
+int fail(nbody_ctx* c, int code, const std::string& msg) {
+	if (c) c->err = msg;
+	g_err = msg;
+	return code;
+}
+#define CK(call)                                                                              \
+	do {                                                                                      \
+		cudaError_t e__ = (call);                                                             \
+		if (e__ != cudaSuccess)                                                               \
+			return fail(ctx, NBODY_ERR_CUDA,                                                  \
+						std::string(#call) + ": " + cudaGetErrorString(e__));                 \
+	} while (0)
+#define CKN(call)                                                                             \
+	do {                                                                                      \
+		ncclResult_t r__ = (call);                                                            \
+		if (r__ != 0)                                                                         \
+			return fail(ctx, NBODY_ERR_NCCL, std::string(#call) + ": " +                      \
+												 g_nccl.GetErrorString(r__));                 \
+	} while (0)
+
+// variant -1 (default) = auto: measured on B200 (tools/sweep.py), the I=4 kernel wins by ~1.5 %
+// once every CTA slot has many units (large owned N); the I=2 / 6-CTAs-per-SM kernel is the
+// robust choice below that.
+const Variant& variant_of(const nbody_ctx* c) {
+	const int nv = c->prec == 64 ? N_VAR64 : N_VAR32;
+	const Variant* tab = c->prec == 64 ? g_var64 : g_var32;
+	long v = c->opt_variant;
+	if (v < 0 || v >= nv) v = (c->prec == 64 && c->own_real >= 200000u) ? 1 : 0;
+	return tab[v];
+}
+
+// j-slices per launch.  Units (i-tile, j-slice) are handed out dynamically, so the tail is
+// about one unit long: aim at >= UNITS_PER_SLOT units per resident CTA, keep a slice at
+// least MIN_TILES tiles long (pipeline prologue + partial-sum traffic), cap the partial buffer.
+unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, long forced) {
+	const unsigned UNITS_PER_SLOT = 40, MIN_TILES = 2;
+	unsigned smax = std::min<unsigned>(MAX_SLICES, std::max(1u, jt_count / MIN_TILES));
+	if (forced > 0) return std::min<unsigned>((unsigned)forced, std::max(1u, jt_count));
+	if (n_itiles == 0) return 1;
+	unsigned want = (UNITS_PER_SLOT * slots + n_itiles - 1) / n_itiles;
+	return std::max(1u, std::min(want, smax));
+}
+}  // namespace
+
+// ------------------------------------------------------------------ helpers on a context
+namespace {
+
+int ensure_apart(nbody_ctx* ctx, unsigned slices) {
+	if (slices <= ctx->apart_slices) return NBODY_OK;
+	CK(cudaStreamSynchronize(ctx->sc));
+	if (ctx->apart) CK(cudaFree(ctx->apart));
+	ctx->apart = nullptr;
+	CK(cudaMalloc(&ctx->apart, (size_t)slices * ctx->own_pad * 4 * ctx->esz));
+	ctx->apart_slices = slices;
+	return NBODY_OK;
+}
+
+struct LaunchPlan {
+	unsigned n_itiles, slots, grid;
+	unsigned s_local, s_remote;	 // slices
+	unsigned jt_total, jt_per_rank;
+};
+
+int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
+	const Variant& v = variant_of(ctx);
+	const unsigned itile = v.threads * v.ipt;
+	const unsigned TJ = 256;
+	lp->n_itiles = (ctx->own_real + itile - 1) / itile;
+	int per_sm = 0;
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, v.fn, v.threads, v.smem));
+	if (per_sm < 1) return fail(ctx, NBODY_ERR_CUDA, "force kernel does not fit on an SM");
+	lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
+	lp->jt_total = ctx->n_pad / TJ;
+	lp->jt_per_rank = ctx->own_pad / TJ;
+	// only tiles that hold real bodies matter for the tail (pad tiles are all-zero-mass),
+	// but keeping them makes the per-rank tile ranges uniform; n_pad - n < world*PAD_UNIT.
+	lp->s_local = choose_slices(lp->n_itiles, lp->jt_per_rank, lp->slots, ctx->opt_slices);
+	lp->s_remote = ctx->world > 1 ? choose_slices(lp->n_itiles, lp->jt_total - lp->jt_per_rank,
+												  lp->slots, ctx->opt_slices)
+								  : 0;
+	return NBODY_OK;
+}
+
+// one force launch over j-tiles [jt_begin, jt_begin + jt_count) (wrapping)
+int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, const void* pos, unsigned jt_begin,
+					   unsigned jt_count, unsigned n_slices, unsigned slice_base) {
+	if (lp.n_itiles == 0 || jt_count == 0) return NBODY_OK;
+	const Variant& v = variant_of(ctx);
+	ForceParams p;
+	p.pos = pos;
+	p.apart = ctx->apart;
+	p.own0 = ctx->own0;
+	p.own_pad = ctx->own_pad;
+	p.n_itiles = lp.n_itiles;
+	p.jt_begin = jt_begin % lp.jt_total;
+	p.jt_count = jt_count;
+	p.jt_total = lp.jt_total;
+	p.n_slices = n_slices;
+	p.slice_base = slice_base;
+	p.counter = ctx->d_counters + (slice_base ? 1 : 0);
+	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
+	const unsigned long long units = (unsigned long long)lp.n_itiles * n_slices;
+	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
+	cudaEvent_t e0 = nullptr, e1 = nullptr;
+	if (ctx->opt_time_kernels) {
+		if (ctx->kev_used + 2 > ctx->kev.size()) {
+			for (int k = 0; k < 2; ++k) {
+				cudaEvent_t e;
+				CK(cudaEventCreate(&e));
+				ctx->kev.push_back(e);
+			}
+		}
+		e0 = ctx->kev[ctx->kev_used++];
+		e1 = ctx->kev[ctx->kev_used++];
+		CK(cudaEventRecord(e0, ctx->sc));
+	}
+	v.launch(dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
+	CK(cudaGetLastError());
+	if (e1) CK(cudaEventRecord(e1, ctx->sc));
+	ctx->tm.force_launches++;
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+
+// all-gather the owned block of `buf` (V4[n_pad]) across ranks on the comm stream,
+// after everything enqueued so far on sc; leaves e_g recorded on sm.
+int enqueue_gather(nbody_ctx* ctx, void* buf) {
+	CK(cudaEventRecord(ctx->e_k2, ctx->sc));
+	CK(cudaStreamWaitEvent(ctx->sm, ctx->e_k2, 0));
+	const size_t bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
+	char* base = (char*)buf;
+	CKN(g_nccl.AllGather(base + (size_t)ctx->rank * bytes, base, bytes, NCCL_INT8, ctx->comm,
+						 ctx->sm));
+	CK(cudaEventRecord(ctx->e_g, ctx->sm));
+	return NBODY_OK;
+}
+
+// acceleration of the owned rows from positions `pos`; the caller has already made the
+// owned block of `pos` current.  need_gather: the other ranks' blocks are stale.
+int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, void* pos, bool need_gather) {
+	int rc;
+	ctx->tm.interactions += (uint64_t)ctx->own_real * (uint64_t)ctx->n;	 // self pairs counted,
+	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
+	if (ctx->world == 1)
+		return launch_force_range(ctx, lp, pos, 0, lp.jt_total, lp.s_local, 0);
+	if (need_gather && (rc = enqueue_gather(ctx, pos))) return rc;
+	// local tiles first: overlaps the all-gather running on sm
+	if ((rc = launch_force_range(ctx, lp, pos, ctx->rank * lp.jt_per_rank, lp.jt_per_rank,
+								 lp.s_local, 0)))
+		return rc;
+	if (need_gather) CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+	return launch_force_range(ctx, lp, pos, (ctx->rank + 1) * lp.jt_per_rank,
+							  lp.jt_total - lp.jt_per_rank, lp.s_remote, lp.s_local);
+}
+
+template <typename T>
+int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_next, double b,
+				 double final_scale, int first, int last) {
+	if (ctx->own_real == 0) return NBODY_OK;
+	StageParams<T> p;
+	p.apart = ctx->apart;
+	p.Y = ctx->Y;
+	p.P = ctx->P;
+	p.vel_n = ctx->vel_n;
+	p.vel_s = ctx->vel_s;
+	p.acc_r = ctx->acc_r;
+	p.acc_v = ctx->acc_v;
+	p.rhs_out = rhs_out;
+	p.own0 = ctx->own0;
+	p.own_pad = ctx->own_pad;
+	p.own_real = ctx->own_real;
+	p.n_slices = lp.s_local + lp.s_remote;
+	p.minusG = (T)(-(T)ctx->G);
+	p.c_next = (T)c_next;
+	p.b = (T)b;
+	p.final_scale = (T)final_scale;
+	p.first = first;
+	p.last = last;
+	stage_kernel<T><<<(ctx->own_real + 255) / 256, 256, 0, ctx->sc>>>(p);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+
+int stage_dispatch(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_next, double b,
+				   double final_scale, int first, int last) {
+	return ctx->prec == 64
+			   ? launch_stage<double>(ctx, lp, rhs_out, c_next, b, final_scale, first, last)
+			   : launch_stage<float>(ctx, lp, rhs_out, c_next, b, final_scale, first, last);
+}
+
+// one integrator step, enqueued on sc (+ sm).  tau, c and b are formed in T exactly as
+// the oracle forms them (tau/2, tau, tau/6 computed in T on the host).
+int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, int scheme, double tau) {
+	int rc;
+	double c[4], b[4], fs;
+	int ns;
+	if (ctx->prec == 64) {
+		if (scheme == NBODY_RK2) { ns = 2; c[0] = tau / 2; b[0] = 0.; b[1] = 1.; fs = tau; }
+		else { ns = 4; c[0] = tau / 2; c[1] = tau / 2; c[2] = tau; b[0] = 1.; b[1] = 2.; b[2] = 2.; b[3] = 1.; fs = tau / 6; }
+	} else {
+		const float t = (float)tau;
+		if (scheme == NBODY_RK2) { ns = 2; c[0] = t / 2; b[0] = 0.; b[1] = 1.; fs = t; }
+		else { ns = 4; c[0] = t / 2; c[1] = t / 2; c[2] = t; b[0] = 1.; b[1] = 2.; b[2] = 2.; b[3] = 1.; fs = t / 6; }
+	}
+	for (int s = 0; s < ns; ++s) {
+		void* pos = s == 0 ? ctx->Y : ctx->P;
+		const bool need_gather = s == 0 ? !ctx->y_gathered : true;
+		if ((rc = enqueue_forces(ctx, lp, pos, need_gather))) return rc;
+		if (s == 0) ctx->y_gathered = true;
+		const int last = s == ns - 1;
+		if ((rc = stage_dispatch(ctx, lp, nullptr, last ? 0. : c[s], b[s], fs, s == 0, last)))
+			return rc;
+	}
+	ctx->y_gathered = ctx->world == 1;
+	return NBODY_OK;
+}
+
+int ensure_y_gathered(nbody_ctx* ctx) {
+	if (ctx->y_gathered) return NBODY_OK;
+	int rc = enqueue_gather(ctx, ctx->Y);
+	if (rc) return rc;
+	CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+	ctx->y_gathered = true;
+	return NBODY_OK;
+}
+}  // namespace
+
+// ------------------------------------------------------------------ the C ABI
+extern "C" {
+
+const char* nbody_version(void) { return "nbody_b200 0.1 (sm_100a)"; }
+
+const char* nbody_last_error(const nbody_ctx* ctx) {
+	return ctx ? ctx->err.c_str() : g_err.c_str();
+}
+
+int nbody_nccl_unique_id(void* out) {
+	nbody_ctx* ctx = nullptr;
+	if (!out) return fail(ctx, NBODY_ERR_ARG, "nbody_nccl_unique_id: null output");
+	if (!g_nccl.load()) return fail(ctx, NBODY_ERR_NCCL, g_nccl.err);
+	ncclUniqueId id;
+	CKN(g_nccl.GetUniqueId(&id));
+	memcpy(out, &id, NBODY_NCCL_UID_BYTES);
+	return NBODY_OK;
+}
+
+void nbody_destroy(nbody_ctx* ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	if (ctx->sc) cudaStreamSynchronize(ctx->sc);
+	if (ctx->sm) cudaStreamSynchronize(ctx->sm);
+	if (ctx->sx) cudaStreamSynchronize(ctx->sx);
+	if (ctx->graph) cudaGraphExecDestroy(ctx->graph);
+	if (ctx->comm && g_nccl.lib) g_nccl.CommDestroy(ctx->comm);
+	void* bufs[] = {ctx->Y, ctx->P, ctx->vel_n, ctx->vel_s, ctx->acc_r, ctx->acc_v, ctx->apart,
+					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters};
+	for (void* b : bufs)
+		if (b) cudaFree(b);
+	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s) {
+		if (ctx->snap_dev[s]) cudaFree(ctx->snap_dev[s]);
+		if (ctx->snap_host[s]) cudaFreeHost(ctx->snap_host[s]);
+		if (ctx->snap_ev[s]) cudaEventDestroy(ctx->snap_ev[s]);
+	}
+	for (cudaEvent_t e : ctx->kev) cudaEventDestroy(e);
+	cudaEvent_t evs[] = {ctx->e_k2, ctx->e_g, ctx->e_snap, ctx->ev_start, ctx->ev_stop};
+	for (cudaEvent_t e : evs)
+		if (e) cudaEventDestroy(e);
+	cudaStream_t ss[] = {ctx->sc, ctx->sm, ctx->sx};
+	for (cudaStream_t s : ss)
+		if (s) cudaStreamDestroy(s);
+	delete ctx;
+}
+
+static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+		return fail(ctx, NBODY_ERR_NO_DEVICE,
+					"no CUDA device: this library has no CPU fallback (sm_100a required)");
+	if (ctx->device < 0 || ctx->device >= ndev)
+		return fail(ctx, NBODY_ERR_ARG, "device index out of range");
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, ctx->device));
+	if (prop.major != 10)
+		return fail(ctx, NBODY_ERR_NO_DEVICE,
+					std::string("device '") + prop.name +
+						"' is not sm_100 (Blackwell B200); the kernels are built for sm_100a only");
+	ctx->n_sm = prop.multiProcessorCount;
+	CK(cudaSetDevice(ctx->device));
+	CK(cudaStreamCreateWithFlags(&ctx->sc, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&ctx->sm, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&ctx->sx, cudaStreamNonBlocking));
+	CK(cudaEventCreateWithFlags(&ctx->e_k2, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&ctx->e_g, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&ctx->e_snap, cudaEventDisableTiming));
+	CK(cudaEventCreate(&ctx->ev_start));
+	CK(cudaEventCreate(&ctx->ev_stop));
+	const size_t v4 = 4 * ctx->esz;
+	CK(cudaMalloc(&ctx->Y, (size_t)ctx->n_pad * v4));
+	CK(cudaMalloc(&ctx->P, (size_t)ctx->n_pad * v4));
+	CK(cudaMalloc(&ctx->vel_n, (size_t)ctx->own_pad * v4));
+	CK(cudaMalloc(&ctx->vel_s, (size_t)ctx->own_pad * v4));
+	CK(cudaMalloc(&ctx->acc_r, (size_t)ctx->own_pad * v4));
+	CK(cudaMalloc(&ctx->acc_v, (size_t)ctx->own_pad * v4));
+	CK(cudaMalloc(&ctx->d_energy, 2 * sizeof(double)));
+	CK(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned)));
+	CK(cudaMemset(ctx->vel_s, 0, (size_t)ctx->own_pad * v4));
+	for (int i = 0; i < N_VAR64; ++i)
+		CK(cudaFuncSetAttribute(g_var64[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+								(int)g_var64[i].smem));
+	for (int i = 0; i < N_VAR32; ++i)
+		CK(cudaFuncSetAttribute(g_var32[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+								(int)g_var32[i].smem));
+	if (ctx->world > 1) {
+		if (!nccl_uid) return fail(ctx, NBODY_ERR_ARG, "world > 1 needs an NCCL unique id");
+		if (!g_nccl.load()) return fail(ctx, NBODY_ERR_NCCL, g_nccl.err);
+		ncclUniqueId id;
+		memcpy(&id, nccl_uid, NBODY_NCCL_UID_BYTES);
+		CKN(g_nccl.CommInitRank(&ctx->comm, ctx->world, id, ctx->rank));
+	}
+	return NBODY_OK;
+}
+
+int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank, int world,
+				 const void* nccl_uid) {
+	if (!out) return fail(nullptr, NBODY_ERR_ARG, "nbody_create: null output");
+	*out = nullptr;
+	if (n == 0) return fail(nullptr, NBODY_ERR_ARG, "nbody_create: n == 0");
+	if (precision != 64 && precision != 32)
+		return fail(nullptr, NBODY_ERR_ARG, "nbody_create: precision must be 64 or 32");
+	if (world < 1 || rank < 0 || rank >= world)
+		return fail(nullptr, NBODY_ERR_ARG, "nbody_create: bad rank/world");
+	if ((size_t)world > n)	// class_Solver_N_body.hpp:115-117
+		return fail(nullptr, NBODY_ERR_ARG,
+					"The number of processes is greater than the problem dimension");
+	if (n > 0x7fffffffu - 2u * PAD_UNIT * (unsigned)world)
+		return fail(nullptr, NBODY_ERR_ARG, "nbody_create: n too large (32-bit row indices)");
+	nbody_ctx* ctx = new nbody_ctx();
+	ctx->n = n;
+	ctx->prec = precision;
+	ctx->esz = precision == 64 ? 8 : 4;
+	ctx->device = device;
+	ctx->rank = rank;
+	ctx->world = world;
+	const size_t per = (n + world - 1) / world;
+	ctx->own_pad = (unsigned)((per + PAD_UNIT - 1) / PAD_UNIT * PAD_UNIT);
+	ctx->n_pad = ctx->own_pad * (unsigned)world;
+	ctx->own0 = ctx->own_pad * (unsigned)rank;
+	ctx->own_real = ctx->own0 >= n ? 0u : (unsigned)std::min<size_t>(ctx->own_pad, n - ctx->own0);
+	int rc = create_impl(ctx, nccl_uid);
+	if (rc != NBODY_OK) {
+		std::string e = ctx->err;
+		nbody_destroy(ctx);
+		g_err = e;
+		return rc;
+	}
+	*out = ctx;
+	return NBODY_OK;
+}
+
+int nbody_set_params(nbody_ctx* ctx, double G, double eps) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	if (!(eps >= 0.)) return fail(ctx, NBODY_ERR_ARG, "eps must be >= 0");
+	ctx->G = G;
+	ctx->eps = eps;
+	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+	return NBODY_OK;
+}
+
+int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
+	if (!ctx || !name) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	std::string k(name);
+	if (k == "time_kernels") ctx->opt_time_kernels = value;
+	else if (k == "slices") ctx->opt_slices = value;
+	else if (k == "variant") {
+		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;
+		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "variant out of range");
+		ctx->opt_variant = value;
+	} else if (k == "use_graph") ctx->opt_use_graph = value;
+	else return fail(ctx, NBODY_ERR_ARG, "unknown option " + k);
+	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+	return NBODY_OK;
+}
+
+int nbody_owned_range(const nbody_ctx* ctx, size_t* begin, size_t* end) {
+	if (!ctx || !begin || !end) return NBODY_ERR_ARG;
+	*begin = std::min<size_t>(ctx->own0, ctx->n);
+	*end = *begin + ctx->own_real;
+	return NBODY_OK;
+}
+
+static int upload_common(nbody_ctx* ctx) {
+	ctx->y_gathered = true;	 // every rank uploaded the whole array
+	ctx->uploaded = true;
+	ctx->tm.steps_done = 0;
+	return NBODY_OK;
+}
+
+int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
+	if (!ctx || !bodies) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	const size_t bytes = ctx->n * 7 * ctx->esz;
+	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes));
+	CK(cudaMemcpyAsync(ctx->d_aos, bodies, bytes, cudaMemcpyHostToDevice, ctx->sc));
+	const unsigned g = (ctx->n_pad + 255) / 256;
+	if (ctx->prec == 64)
+		pack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>((const double*)ctx->d_aos, ctx->Y, ctx->P,
+														ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+														ctx->own0, ctx->own_pad);
+	else
+		pack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>((const float*)ctx->d_aos, ctx->Y, ctx->P,
+													   ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+													   ctx->own0, ctx->own_pad);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	CK(cudaStreamSynchronize(ctx->sc));	 // the host buffer is borrowed for the call only
+	return upload_common(ctx);
+}
+
+int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* v4) {
+	if (!ctx || !m || !r4 || !v4) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	const size_t e = ctx->esz, n = ctx->n;
+	const size_t bytes = n * 9 * e;	 // m | r4 | v4
+	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, std::max(bytes, n * 7 * e) + 64));
+	else {
+		CK(cudaFree(ctx->d_aos));
+		ctx->d_aos = nullptr;
+		CK(cudaMalloc(&ctx->d_aos, std::max(bytes, n * 7 * e) + 64));
+	}
+	char* d = (char*)ctx->d_aos;
+	char* dr = d + (n * e + 31) / 32 * 32;
+	char* dv = dr + n * 4 * e;
+	CK(cudaMemcpyAsync(d, m, n * e, cudaMemcpyHostToDevice, ctx->sc));
+	CK(cudaMemcpyAsync(dr, r4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
+	CK(cudaMemcpyAsync(dv, v4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
+	const unsigned g = (ctx->n_pad + 255) / 256;
+	if (ctx->prec == 64)
+		pack_soa_kernel<double><<<g, 256, 0, ctx->sc>>>((const double*)d, dr, dv, ctx->Y, ctx->P,
+														ctx->vel_n, (unsigned)n, ctx->n_pad,
+														ctx->own0, ctx->own_pad);
+	else
+		pack_soa_kernel<float><<<g, 256, 0, ctx->sc>>>((const float*)d, dr, dv, ctx->Y, ctx->P,
+													   ctx->vel_n, (unsigned)n, ctx->n_pad,
+													   ctx->own0, ctx->own_pad);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	CK(cudaStreamSynchronize(ctx->sc));
+	return upload_common(ctx);
+}
+
+static int begin_timed_call(nbody_ctx* ctx) {
+	ctx->tm.force_launches = 0;
+	ctx->tm.interactions = 0;
+	ctx->tm.force_ms = 0;
+	ctx->kev_used = 0;
+	CK(cudaEventRecord(ctx->ev_start, ctx->sc));
+	return NBODY_OK;
+}
+static int end_timed_call(nbody_ctx* ctx) {
+	CK(cudaEventRecord(ctx->ev_stop, ctx->sc));
+	ctx->timing_pending = true;
+	return NBODY_OK;
+}
+
+int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
+	if (!ctx || !acc_host) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_rhs before upload");
+	CK(cudaSetDevice(ctx->device));
+	LaunchPlan lp;
+	int rc;
+	if ((rc = make_plan(ctx, &lp))) return rc;
+	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
+	if (!ctx->rhs_out) CK(cudaMalloc(&ctx->rhs_out, (size_t)ctx->own_pad * 3 * ctx->esz));
+	if ((rc = begin_timed_call(ctx))) return rc;
+	if ((rc = enqueue_forces(ctx, lp, ctx->Y, !ctx->y_gathered))) return rc;
+	ctx->y_gathered = true;
+	if ((rc = stage_dispatch(ctx, lp, ctx->rhs_out, 0., 0., 0., 1, 0))) return rc;
+	if ((rc = end_timed_call(ctx))) return rc;
+	if (ctx->own_real)
+		CK(cudaMemcpyAsync((char*)acc_host + (size_t)ctx->own0 * 3 * ctx->esz, ctx->rhs_out,
+						   (size_t)ctx->own_real * 3 * ctx->esz, cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	return NBODY_OK;
+}
+
+int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	if (scheme != NBODY_RK2 && scheme != NBODY_RK4)
+		return fail(ctx, NBODY_ERR_ARG, "scheme must be 2 (RK2) or 4 (RK4)");
+	if (n_steps < 0) return fail(ctx, NBODY_ERR_ARG, "n_steps < 0");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step before upload");
+	CK(cudaSetDevice(ctx->device));
+	LaunchPlan lp;
+	int rc;
+	if ((rc = make_plan(ctx, &lp))) return rc;
+	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
+	if ((rc = begin_timed_call(ctx))) return rc;
+	long done = 0;
+	// Launch-bound regime (small n, single rank): replay one captured step as a CUDA graph.
+	if (ctx->opt_use_graph && ctx->world == 1 && !ctx->opt_time_kernels && n_steps > 1) {
+		if (!ctx->graph || ctx->graph_scheme != scheme || ctx->graph_tau != tau) {
+			if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+			cudaGraph_t g = nullptr;
+			const nbody_timing keep = ctx->tm;
+			CK(cudaStreamBeginCapture(ctx->sc, cudaStreamCaptureModeThreadLocal));
+			rc = enqueue_step(ctx, lp, scheme, tau);
+			cudaError_t ce = cudaStreamEndCapture(ctx->sc, &g);
+			ctx->tm = keep;
+			if (rc) return rc;
+			CK(ce);
+			CK(cudaGraphInstantiate(&ctx->graph, g, 0));
+			cudaGraphDestroy(g);
+			ctx->graph_scheme = scheme;
+			ctx->graph_tau = tau;
+		}
+		const int ns = scheme == NBODY_RK2 ? 2 : 4;
+		for (; done < n_steps; ++done) {
+			CK(cudaGraphLaunch(ctx->graph, ctx->sc));
+			ctx->tm.force_launches += ns;
+			ctx->tm.total_launches += 2 * ns;
+			ctx->tm.interactions += (uint64_t)ns * ctx->own_real * ctx->n;
+		}
+	}
+	for (; done < n_steps; ++done)
+		if ((rc = enqueue_step(ctx, lp, scheme, tau))) return rc;
+	ctx->tm.steps_done += (uint64_t)n_steps;
+	return end_timed_call(ctx);
+}
+
+int nbody_sync(nbody_ctx* ctx) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	CK(cudaSetDevice(ctx->device));
+	CK(cudaStreamSynchronize(ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sm));
+	return NBODY_OK;
+}
+
+int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
+	if (!ctx || !out) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	if (ctx->timing_pending) {
+		CK(cudaEventSynchronize(ctx->ev_stop));
+		float ms = 0;
+		CK(cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
+		ctx->tm.last_call_ms = ms;
+		double f = 0;
+		for (size_t k = 0; k + 1 < ctx->kev_used; k += 2) {
+			float t = 0;
+			CK(cudaEventElapsedTime(&t, ctx->kev[k], ctx->kev[k + 1]));
+			f += t;
+		}
+		ctx->tm.force_ms = f;
+		ctx->timing_pending = false;
+	}
+	*out = ctx->tm;
+	return NBODY_OK;
+}
+
+// ------------------------------------------------------------------ K4: snapshots
+int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
+	if (!ctx || !ticket) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "snapshot before upload");
+	CK(cudaSetDevice(ctx->device));
+	int slot = -1;
+	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s)
+		if (!ctx->snap_state[s]) { slot = s; break; }
+	if (slot < 0) return fail(ctx, NBODY_ERR_STATE, "all snapshot slots are held");
+	const size_t bytes = ctx->n * 3 * ctx->esz;
+	if (!ctx->snap_dev[slot]) {
+		CK(cudaMalloc(&ctx->snap_dev[slot], bytes));
+		CK(cudaHostAlloc(&ctx->snap_host[slot], bytes, cudaHostAllocDefault));
+		CK(cudaEventCreateWithFlags(&ctx->snap_ev[slot], cudaEventDisableTiming));
+	}
+	int rc;
+	if ((rc = ensure_y_gathered(ctx))) return rc;
+	const unsigned g = ((unsigned)ctx->n + 255) / 256;
+	if (ctx->prec == 64)
+		snapshot_pack_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, (double*)ctx->snap_dev[slot],
+															 (unsigned)ctx->n);
+	else
+		snapshot_pack_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, (float*)ctx->snap_dev[slot],
+															(unsigned)ctx->n);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	CK(cudaEventRecord(ctx->e_snap, ctx->sc));
+	CK(cudaStreamWaitEvent(ctx->sx, ctx->e_snap, 0));
+	CK(cudaMemcpyAsync(ctx->snap_host[slot], ctx->snap_dev[slot], bytes, cudaMemcpyDeviceToHost,
+					   ctx->sx));
+	CK(cudaEventRecord(ctx->snap_ev[slot], ctx->sx));
+	ctx->snap_state[slot] = 1;
+	ctx->snap_ticket[slot] = ctx->next_ticket++;
+	*ticket = ctx->snap_ticket[slot];
+	return NBODY_OK;
+}
+
+static int find_slot(nbody_ctx* ctx, uint64_t ticket) {
+	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s)
+		if (ctx->snap_state[s] && ctx->snap_ticket[s] == ticket) return s;
+	return -1;
+}
+
+int nbody_snapshot_wait(nbody_ctx* ctx, uint64_t ticket, const void** r_host) {
+	if (!ctx || !r_host) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	const int s = find_slot(ctx, ticket);
+	if (s < 0) return fail(ctx, NBODY_ERR_ARG, "unknown snapshot ticket");
+	CK(cudaEventSynchronize(ctx->snap_ev[s]));
+	*r_host = ctx->snap_host[s];
+	return NBODY_OK;
+}
+
+int nbody_snapshot_release(nbody_ctx* ctx, uint64_t ticket) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	const int s = find_slot(ctx, ticket);
+	if (s < 0) return fail(ctx, NBODY_ERR_ARG, "unknown snapshot ticket");
+	CK(cudaEventSynchronize(ctx->snap_ev[s]));
+	ctx->snap_state[s] = 0;
+	return NBODY_OK;
+}
+
+// ------------------------------------------------------------------ download / energy
+int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
+	if (!ctx || !bodies) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "download before upload");
+	CK(cudaSetDevice(ctx->device));
+	int rc;
+	if ((rc = ensure_y_gathered(ctx))) return rc;
+	const size_t v4 = 4 * ctx->esz;
+	const void* vel = ctx->vel_n;
+	if (ctx->world > 1) {
+		if (!ctx->vel_all) CK(cudaMalloc(&ctx->vel_all, (size_t)ctx->n_pad * v4));
+		CK(cudaMemcpyAsync((char*)ctx->vel_all + (size_t)ctx->own0 * v4, ctx->vel_n,
+						   (size_t)ctx->own_pad * v4, cudaMemcpyDeviceToDevice, ctx->sc));
+		if ((rc = enqueue_gather(ctx, ctx->vel_all))) return rc;
+		CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+		vel = ctx->vel_all;
+	}
+	const size_t bytes = ctx->n * 7 * ctx->esz;
+	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes + 64));
+	const unsigned g = ((unsigned)ctx->n + 255) / 256;
+	if (ctx->prec == 64)
+		unpack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, vel, (double*)ctx->d_aos,
+														  (unsigned)ctx->n);
+	else
+		unpack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, vel, (float*)ctx->d_aos,
+														 (unsigned)ctx->n);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	CK(cudaMemcpyAsync(bodies, ctx->d_aos, bytes, cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	return NBODY_OK;
+}
+
+int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential) {
+	if (!ctx || !kinetic || !potential) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "energy before upload");
+	CK(cudaSetDevice(ctx->device));
+	int rc;
+	if ((rc = ensure_y_gathered(ctx))) return rc;
+	CK(cudaMemsetAsync(ctx->d_energy, 0, 2 * sizeof(double), ctx->sc));
+	if (ctx->own_real) {
+		const unsigned g = (ctx->own_real + 255) / 256;
+		if (ctx->prec == 64)
+			energy_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
+														  ctx->own0, ctx->own_real, ctx->eps,
+														  ctx->G, ctx->d_energy);
+		else
+			energy_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
+														 ctx->own0, ctx->own_real, ctx->eps,
+														 ctx->G, ctx->d_energy);
+		CK(cudaGetLastError());
+		ctx->tm.total_launches++;
+	}
+	if (ctx->world > 1)
+		CKN(g_nccl.AllReduce(ctx->d_energy, ctx->d_energy, 2, NCCL_DOUBLE, NCCL_SUM, ctx->comm,
+							 ctx->sc));
+	double h[2];
+	CK(cudaMemcpyAsync(h, ctx->d_energy, sizeof(h), cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	*kinetic = h[0];
+	*potential = h[1];
+	return NBODY_OK;
+}
+
+// ------------------------------------------------------------------ misc
+void* nbody_host_alloc(size_t bytes) {
+	void* p = nullptr;
+	if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+	return p;
+}
+void nbody_host_free(void* p) {
+	if (p) cudaFreeHost(p);
+}
+
+int nbody_measure_fma_peak(int device, int precision, double ms_target, double* tflops) {
+	nbody_ctx* ctx = nullptr;
+	if (!tflops || (precision != 64 && precision != 32))
+		return fail(ctx, NBODY_ERR_ARG, "nbody_measure_fma_peak: bad argument");
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+		return fail(ctx, NBODY_ERR_NO_DEVICE, "no such CUDA device");
+	CK(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, device));
+	const int blocks = prop.multiProcessorCount * 8, threads = 256;
+	void* d = nullptr;
+	CK(cudaMalloc(&d, 64));
+	cudaEvent_t e0, e1;
+	CK(cudaEventCreate(&e0));
+	CK(cudaEventCreate(&e1));
+	int iters = 256;
+	float ms = 0;
+	for (int pass = 0; pass < 8; ++pass) {
+		CK(cudaEventRecord(e0, 0));
+		if (precision == 64)
+			fma_peak_kernel<double><<<blocks, threads>>>((double*)d, 0.999999, 1e-9, iters);
+		else
+			fma_peak_kernel<float><<<blocks, threads>>>((float*)d, 0.9999f, 1e-5f, iters);
+		CK(cudaEventRecord(e1, 0));
+		CK(cudaEventSynchronize(e1));
+		CK(cudaGetLastError());
+		CK(cudaEventElapsedTime(&ms, e0, e1));
+		if (ms >= ms_target * 0.7) break;
+		const double scale = ms > 0.05 ? ms_target / ms : 16.0;
+		iters = (int)std::min(2.0e9 / 128, std::max(1.0, iters * std::min(scale, 64.0)));
+	}
+	const double flops = 2.0 * 8 * 16 * (double)iters * (double)blocks * threads;
+	*tflops = flops / (ms * 1e-3) / 1e12;
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	cudaFree(d);
+	return NBODY_OK;
+}
+
+}  // extern "C"

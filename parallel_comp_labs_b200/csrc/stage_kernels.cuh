@@ -1,0 +1,283 @@
+// stage_kernels.cuh -- K2 (fused RK stage), layout kernels, K4 snapshot pack, diagnostics.
+//
+// K2 replaces, in ONE launch per RK stage over the owned rows:
+//   CPU  mult/add lambdas + copy_n          lab_4 .../schemes/ode_RK2_MPI.hpp:26-43,74-90
+//   GPU  4x mult_n_add + 2x D2D k_r <- v    lab_5 N_body.cu:120-127,202,305-316
+// plus the j-slice reduction and the "a_tmp *= -G" of the RHS
+//   (lab_4 .../struct_ode_system.hpp:73), so every state word is read once and written
+// once per stage.  Rounding sequence == oracle/nbody_oracle.c (mult, then add; no FMA
+// contraction): for RK2 this reproduces the reference's stage arithmetic bit-for-bit
+// given the same accelerations.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "force_kernels.cuh"
+
+namespace nbody {
+
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+
+template <typename T>
+struct StageParams {
+	const void* apart;	// V4[n_slices][own_pad] raw partial sums from K1
+	void* Y;			// V4[n_pad]   y_n positions + mass (full array)
+	void* P;			// V4[n_pad]   stage positions + mass (full array, gather target)
+	void* vel_n;		// V4[own_pad] y_n velocities (owned rows)
+	void* vel_s;		// V4[own_pad] stage velocities (owned rows)
+	void* acc_r;		// V4[own_pad] running sum b_s k_s (positions part)
+	void* acc_v;		// V4[own_pad]                    (velocities part)
+	void* rhs_out;		// optional T[3*own_real]: -G*sum only (nbody_rhs test hook)
+	unsigned own0, own_pad, own_real, n_slices;
+	T minusG;		 // -G
+	T c_next;		 // a_{s+1,s} * tau (tau/2, tau/2, tau for RK4; tau/2 for RK2)
+	T b;			 // weight of this stage in the final combination
+	T final_scale;	 // tau/6 (RK4) or tau (RK2)
+	int first, last;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
+	typedef typename V4<T>::type vec4;
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= p.own_real) return;
+	const vec4* apart = reinterpret_cast<const vec4*>(p.apart);
+	// fixed-order slice reduction, then a *= -G (struct_ode_system.hpp:73)
+	T ax = T(0), ay = T(0), az = T(0);
+	for (unsigned s = 0; s < p.n_slices; ++s) {
+		const vec4 q = apart[(size_t)s * p.own_pad + i];
+		ax = add_rn(ax, q.x);
+		ay = add_rn(ay, q.y);
+		az = add_rn(az, q.z);
+	}
+	ax = mul_rn(ax, p.minusG);
+	ay = mul_rn(ay, p.minusG);
+	az = mul_rn(az, p.minusG);
+	if (p.rhs_out) {
+		T* o = reinterpret_cast<T*>(p.rhs_out);
+		o[3 * (size_t)i + 0] = ax;
+		o[3 * (size_t)i + 1] = ay;
+		o[3 * (size_t)i + 2] = az;
+		return;
+	}
+	vec4* Y = reinterpret_cast<vec4*>(p.Y);
+	vec4* P = reinterpret_cast<vec4*>(p.P);
+	vec4* vel_n = reinterpret_cast<vec4*>(p.vel_n);
+	vec4* vel_s = reinterpret_cast<vec4*>(p.vel_s);
+	vec4* acc_r = reinterpret_cast<vec4*>(p.acc_r);
+	vec4* acc_v = reinterpret_cast<vec4*>(p.acc_v);
+
+	const vec4 yn = Y[(size_t)p.own0 + i];
+	const vec4 vn = vel_n[i];
+	const vec4 vs = p.first ? vn : vel_s[i];  // k_s.r = stage velocity (diff.r = traj.v)
+
+	// acc (+)= b * k_s
+	vec4 ar, av;
+	ar.x = mul_rn(vs.x, p.b); ar.y = mul_rn(vs.y, p.b); ar.z = mul_rn(vs.z, p.b); ar.w = T(0);
+	av.x = mul_rn(ax, p.b);   av.y = mul_rn(ay, p.b);   av.z = mul_rn(az, p.b);   av.w = T(0);
+	if (!p.first) {
+		const vec4 pr = acc_r[i], pv = acc_v[i];
+		ar.x = add_rn(pr.x, ar.x); ar.y = add_rn(pr.y, ar.y); ar.z = add_rn(pr.z, ar.z);
+		av.x = add_rn(pv.x, av.x); av.y = add_rn(pv.y, av.y); av.z = add_rn(pv.z, av.z);
+	}
+	if (!p.last) {
+		acc_r[i] = ar;
+		acc_v[i] = av;
+		// next stage state: tmp = y_n + (c * k_s)
+		vec4 rn, vnext;
+		rn.x = add_rn(yn.x, mul_rn(vs.x, p.c_next));
+		rn.y = add_rn(yn.y, mul_rn(vs.y, p.c_next));
+		rn.z = add_rn(yn.z, mul_rn(vs.z, p.c_next));
+		rn.w = yn.w;
+		vnext.x = add_rn(vn.x, mul_rn(ax, p.c_next));
+		vnext.y = add_rn(vn.y, mul_rn(ay, p.c_next));
+		vnext.z = add_rn(vn.z, mul_rn(az, p.c_next));
+		vnext.w = T(0);
+		P[(size_t)p.own0 + i] = rn;
+		vel_s[i] = vnext;
+	} else {
+		// y_{n+1} = y_n + (final_scale * acc)
+		vec4 rn, vnew;
+		rn.x = add_rn(yn.x, mul_rn(ar.x, p.final_scale));
+		rn.y = add_rn(yn.y, mul_rn(ar.y, p.final_scale));
+		rn.z = add_rn(yn.z, mul_rn(ar.z, p.final_scale));
+		rn.w = yn.w;
+		vnew.x = add_rn(vn.x, mul_rn(av.x, p.final_scale));
+		vnew.y = add_rn(vn.y, mul_rn(av.y, p.final_scale));
+		vnew.z = add_rn(vn.z, mul_rn(av.z, p.final_scale));
+		vnew.w = T(0);
+		Y[(size_t)p.own0 + i] = rn;
+		vel_n[i] = vnew;
+	}
+}
+
+// ---------------------------------------------------------------- layout kernels
+// AoS Body<T> (7 x T) -> packed {x,y,z,m} for all n bodies and {vx,vy,vz,0} for owned rows.
+template <typename T>
+__global__ void pack_aos_kernel(const T* __restrict__ aos, void* Yv, void* Pv, void* velv,
+								unsigned n, unsigned n_pad, unsigned own0, unsigned own_pad) {
+	typedef typename V4<T>::type vec4;
+	vec4* Y = reinterpret_cast<vec4*>(Yv);
+	vec4* P = reinterpret_cast<vec4*>(Pv);
+	vec4* vel = reinterpret_cast<vec4*>(velv);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_pad) return;
+	vec4 q, v;
+	if (i < n) {
+		const T* b = aos + 7 * (size_t)i;
+		q.x = b[1]; q.y = b[2]; q.z = b[3]; q.w = b[0];
+		v.x = b[4]; v.y = b[5]; v.z = b[6]; v.w = T(0);
+	} else {  // zero-mass pad body at the origin: contributes exactly 0 to every sum
+		q.x = q.y = q.z = q.w = T(0);
+		v.x = v.y = v.z = v.w = T(0);
+	}
+	Y[i] = q;
+	P[i] = q;
+	if (i >= own0 && i < own0 + own_pad) vel[i - own0] = v;
+}
+
+// lab_5 SoA (T m[n], T3 r[n], T3 v[n]) -> packed
+template <typename T>
+__global__ void pack_soa_kernel(const T* __restrict__ m, const void* r4v, const void* v4v,
+								void* Yv, void* Pv, void* velv, unsigned n, unsigned n_pad,
+								unsigned own0, unsigned own_pad) {
+	typedef typename V4<T>::type vec4;
+	const vec4* r4 = reinterpret_cast<const vec4*>(r4v);
+	const vec4* v4 = reinterpret_cast<const vec4*>(v4v);
+	vec4* Y = reinterpret_cast<vec4*>(Yv);
+	vec4* P = reinterpret_cast<vec4*>(Pv);
+	vec4* vel = reinterpret_cast<vec4*>(velv);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_pad) return;
+	vec4 q, v;
+	if (i < n) {
+		q = r4[i];
+		q.w = m[i];
+		v = v4[i];
+		v.w = T(0);
+	} else {
+		q.x = q.y = q.z = q.w = T(0);
+		v.x = v.y = v.z = v.w = T(0);
+	}
+	Y[i] = q;
+	P[i] = q;
+	if (i >= own0 && i < own0 + own_pad) vel[i - own0] = v;
+}
+
+// packed -> AoS Body<T>; vel_all is V4[n_pad] (gathered velocities)
+template <typename T>
+__global__ void unpack_aos_kernel(const void* Yv, const void* velv, T* __restrict__ aos,
+								  unsigned n) {
+	typedef typename V4<T>::type vec4;
+	const vec4* Y = reinterpret_cast<const vec4*>(Yv);
+	const vec4* vel = reinterpret_cast<const vec4*>(velv);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const vec4 q = Y[i], v = vel[i];
+	T* b = aos + 7 * (size_t)i;
+	b[0] = q.w; b[1] = q.x; b[2] = q.y; b[3] = q.z;
+	b[4] = v.x; b[5] = v.y; b[6] = v.z;
+}
+
+// K4: packed positions -> dense T[3n] staging for the pinned-host snapshot ring
+template <typename T>
+__global__ void snapshot_pack_kernel(const void* Yv, T* __restrict__ out, unsigned n) {
+	typedef typename V4<T>::type vec4;
+	const vec4* Y = reinterpret_cast<const vec4*>(Yv);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const vec4 q = Y[i];
+	out[3 * (size_t)i + 0] = q.x;
+	out[3 * (size_t)i + 1] = q.y;
+	out[3 * (size_t)i + 2] = q.z;
+}
+
+// ---------------------------------------------------------------- diagnostics
+// Energy (not in the reference): owned rows i against all j > i (global
+// index), potential consistent with the clamp force.  Always accumulated in FP64.
+// out[0] += kinetic, out[1] += potential (atomicAdd on doubles; diagnostic only).
+template <typename T>
+__global__ void __launch_bounds__(256)
+	energy_kernel(const void* Yv, const void* velv, unsigned n, unsigned own0, unsigned own_real,
+				  double eps, double G, double* out) {
+	typedef typename V4<T>::type vec4;
+	const vec4* Y = reinterpret_cast<const vec4*>(Yv);
+	const vec4* vel = reinterpret_cast<const vec4*>(velv);
+	__shared__ double4 sh[256];
+	__shared__ double red[2][8];
+	const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+	const unsigned gi = own0 + li;
+	const bool live = li < own_real;
+	double xi = 0, yi = 0, zi = 0, mi = 0, kin = 0, u = 0;
+	if (live) {
+		const vec4 q = Y[gi];
+		const vec4 v = vel[li];
+		xi = q.x; yi = q.y; zi = q.z; mi = q.w;
+		kin = 0.5 * mi * ((double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z);
+	}
+	const double eps2 = eps * eps, ie3 = 1.0 / (2.0 * eps * eps * eps);
+	const unsigned jstart = (own0 + blockIdx.x * blockDim.x) & ~255u;  // first tile with j > some i
+	for (unsigned j0 = jstart; j0 < n; j0 += 256) {
+		const unsigned j = j0 + threadIdx.x;
+		double4 s = make_double4(0, 0, 0, 0);
+		if (j < n) {
+			const vec4 q = Y[j];
+			s = make_double4(q.x, q.y, q.z, q.w);
+		}
+		__syncthreads();
+		sh[threadIdx.x] = s;
+		__syncthreads();
+		if (live) {
+			const unsigned lim = min(256u, n - j0);
+			for (unsigned k = 0; k < lim; ++k) {
+				if (j0 + k <= gi) continue;
+				const double4 b = sh[k];
+				const double dx = xi - b.x, dy = yi - b.y, dz = zi - b.z;
+				const double r2 = dx * dx + dy * dy + dz * dz;
+				u += (r2 >= eps2) ? b.w * rsqrt(r2) : b.w * (3.0 * eps2 - r2) * ie3;
+			}
+		}
+	}
+	double pot = -G * mi * u;
+	for (int o = 16; o > 0; o >>= 1) {
+		kin += __shfl_down_sync(0xffffffffu, kin, o);
+		pot += __shfl_down_sync(0xffffffffu, pot, o);
+	}
+	const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+	if (l == 0) {
+		red[0][w] = kin;
+		red[1][w] = pot;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		double k = 0, q = 0;
+		for (int a = 0; a < 8; ++a) {
+			k += red[0][a];
+			q += red[1][a];
+		}
+		atomicAdd(out + 0, k);
+		atomicAdd(out + 1, q);
+	}
+}
+
+// FMA-pipe peak microbenchmark: 8 independent dependent-chains per thread, register
+// resident, no memory traffic.  flops = 2 * 8 * iters * threads.
+template <typename T>
+__global__ void __launch_bounds__(256) fma_peak_kernel(T* out, T a, T b, int iters) {
+	T c0 = T(threadIdx.x), c1 = c0 + T(1), c2 = c0 + T(2), c3 = c0 + T(3);
+	T c4 = c0 + T(4), c5 = c0 + T(5), c6 = c0 + T(6), c7 = c0 + T(7);
+	for (int i = 0; i < iters; ++i) {
+#pragma unroll
+		for (int u = 0; u < 16; ++u) {
+			c0 = fma(c0, a, b); c1 = fma(c1, a, b); c2 = fma(c2, a, b); c3 = fma(c3, a, b);
+			c4 = fma(c4, a, b); c5 = fma(c5, a, b); c6 = fma(c6, a, b); c7 = fma(c7, a, b);
+		}
+	}
+	T s = ((c0 + c1) + (c2 + c3)) + ((c4 + c5) + (c6 + c7));
+	if (s == T(-12345.678)) out[0] = s;	 // never true; keeps the chains alive
+}
+
+}  // namespace nbody

@@ -1,0 +1,463 @@
+// nbody_host.hpp -- C++ host side of the B200 N-body path: the lab's own interface
+// (same type and function names, argument meaning, file formats and error behaviour)
+// re-implemented over the C ABI of include/nbody_b200.h.  Nothing here computes forces
+// or integrates: that is the CUDA library's job, and there is no CPU fallback.
+//
+// Reference interfaces mirrored (file:line relative to the reference root):
+//   Body<T>                               lab_4 .../struct_Body.hpp:5-10
+//   read_data<T>, write_bodies_coords     lab_4 .../utils/read_write_utils.hpp:12-52
+//   ode_system<T> + two factories         lab_4 .../struct_ode_system.hpp:20-134
+//   Solver_N_body<T>::solve_parallel_MPI  lab_4 .../class_Solver_N_body.hpp:87-208
+//   time loop / loop control              lab_4 .../schemes/ode_RK2_MPI.hpp:55-104
+//   ode_RK2_CUDA(m,r,v,t0,t1,tau,p,p1)    lab_5 N_body.cu:208-406
+#pragma once
+#include <array>
+#include <atomic>
+#include <charconv>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <type_traits>
+#include <vector>
+
+#include "nbody_b200.h"
+
+namespace nbody_host {
+
+template <typename T>
+struct Body {  // memory image identical to the reference's: 7 x T, no padding
+	T m;
+	std::array<T, 3> r;
+	std::array<T, 3> v;
+};
+static_assert(sizeof(Body<double>) == 56 && sizeof(Body<float>) == 28, "Body<T> must be packed");
+
+// lab_5's T3 (float4 / double4 used as a 3-vector, .w ignored)
+template <typename T>
+struct alignas(4 * sizeof(T) > 16 ? 16 : 4 * sizeof(T)) Vec4 {
+	T x, y, z, w;
+};
+
+// ---- input ---------------------------------------------------------------------------
+// "N" then N records "m x y z vx vy vz", any whitespace (tabs, CRLF).  Unopenable file:
+// prints the reference's message and throws int 1 (read_write_utils.hpp:15-19).
+template <typename T>
+std::vector<Body<T>> read_data(const std::string& path) {
+	std::ifstream in(path, std::ios::binary);
+	if (!in.is_open()) {
+		std::cout << "file is't open" << std::endl;
+		throw 1;
+	}
+	std::string text((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+	const char* p = text.data();
+	const char* end = p + text.size();
+	auto skip = [&] { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r' || *p == '\f' || *p == '\v')) ++p; };
+	auto next = [&](double& out) {
+		skip();
+		if (p < end && *p == '+') ++p;
+		auto res = std::from_chars(p, end, out);
+		if (res.ec != std::errc()) return false;
+		p = res.ptr;
+		return true;
+	};
+	double nn = 0;
+	std::vector<Body<T>> bodies;
+	if (!next(nn) || nn < 0) return bodies;
+	const std::size_t n = (std::size_t)nn;
+	bodies.reserve(n);
+	Body<T> b{};  // like operator>>, a short file leaves later records at the last value
+	for (std::size_t i = 0; i < n; ++i) {
+		double f[7];
+		bool ok = true;
+		for (int k = 0; k < 7 && ok; ++k) ok = next(f[k]);
+		if (ok) {
+			b.m = (T)f[0];
+			for (int k = 0; k < 3; ++k) {
+				b.r[k] = (T)f[1 + k];
+				b.v[k] = (T)f[4 + k];
+			}
+		}
+		bodies.push_back(b);
+	}
+	return bodies;
+}
+
+// ---- output --------------------------------------------------------------------------
+// Appends "%.16e" of x (17 significant digits, at least 2 exponent digits) + ';'.
+inline void append_sci16(std::string& s, double x) {
+	char buf[40];
+	auto res = std::to_chars(buf, buf + sizeof(buf), x, std::chars_format::scientific, 16);
+	s.append(buf, res.ptr);
+	s.push_back(';');
+}
+
+// One row "t;x1;y1;z1;...;zN;\n" (write_bodies_coords, read_write_utils.hpp:42-52);
+// `pos` is n x 3.  The row is flushed like std::endl does.
+template <typename T>
+void write_positions_row(std::ostream& out, double time, const T* pos, std::size_t n) {
+	std::string row;
+	row.reserve(24 * (3 * n + 1) + 2);
+	append_sci16(row, time);
+	for (std::size_t i = 0; i < 3 * n; ++i) append_sci16(row, (double)pos[i]);
+	row.push_back('\n');
+	out.write(row.data(), (std::streamsize)row.size());
+	out.flush();
+}
+
+template <typename T>
+void write_bodies_coords(std::ostream& out, double time, const std::vector<Body<T>>& bodies) {
+	std::vector<T> pos(3 * bodies.size());
+	for (std::size_t i = 0; i < bodies.size(); ++i)
+		for (int k = 0; k < 3; ++k) pos[3 * i + k] = bodies[i].r[k];
+	write_positions_row(out, time, pos.data(), bodies.size());
+}
+
+inline const char* lab4_header() {	// ode_RK2_MPI.hpp:52 (hard-coded for 4 bodies)
+	return "time;r11;r12;r13;r21;r22;r23;r31;r32;r33;r41;r42;r43\n";
+}
+inline std::string lab5_header(std::size_t n) {	 // N_body.cu:236-246
+	std::string h = "time;";
+	for (std::size_t i = 1; i <= n; ++i)
+		for (int j = 1; j <= 3; ++j) {
+			h += "r_" + std::to_string(i) + "_" + std::to_string(j);
+			h += (i == n && j == 3) ? "\n" : ";";
+		}
+	return h;
+}
+
+// Final state in the INPUT format (restartable runs; SURVEY.md 5 "checkpoint").
+template <typename T>
+void write_input_format(const std::string& path, const std::vector<Body<T>>& bodies) {
+	std::ofstream out(path);
+	out << bodies.size() << "\n";
+	char buf[40];
+	std::string line;
+	for (const auto& b : bodies) {
+		line.clear();
+		const double f[7] = {(double)b.m, (double)b.r[0], (double)b.r[1], (double)b.r[2],
+							 (double)b.v[0], (double)b.v[1], (double)b.v[2]};
+		for (int k = 0; k < 7; ++k) {
+			auto res = std::to_chars(buf, buf + sizeof(buf), f[k], std::chars_format::scientific, 16);
+			line.append(buf, res.ptr);
+			line.push_back(k == 6 ? '\n' : '\t');
+		}
+		out << line;
+	}
+}
+
+// ---- problem descriptor ------------------------------------------------------------------
+template <typename T>
+struct ode_system {
+	T tau = T(0.1);
+	T t_start = 0, t_final = 1;
+	int n_time_steps = 10, N_bodies = 0;
+	std::vector<Body<T>> traj_init;
+	std::string name;
+	// the RHS lambda's captures (struct_ode_system.hpp:53): the operator itself lives on
+	// the GPU behind nbody_rhs / nbody_step
+	T eps = T(1e-6), G = T(6.67e-11);
+
+	// struct_ode_system.hpp:34-81
+	ode_system<T>& ode_system_default_test(const T time_step = 0.1, const T eps_ = 1e-6,
+										   const T G_ = 6.67e-11,
+										   const std::string& path =
+											   "./include/N_body/N_body_config/4body.txt") {
+		name = "4Body_test";
+		t_start = 0.;
+		t_final = 20.;
+		tau = time_step;
+		n_time_steps = (int)((t_final - t_start) / tau);
+		traj_init = read_data<T>(path);
+		N_bodies = (int)traj_init.size();
+		eps = eps_;
+		G = G_;
+		return *this;
+	}
+	// struct_ode_system.hpp:84-133; N_of_bodies is ignored as in the reference
+	ode_system<T>& ode_system_random_data(const std::size_t N_of_bodies, const T time_step,
+										  const T eps_, const T G_, const std::string& path) {
+		name = "4Body_random";
+		t_start = 0.;
+		t_final = 1.;
+		tau = time_step;
+		n_time_steps = (int)((t_final - t_start) / tau);
+		N_bodies = (int)N_of_bodies;
+		traj_init = read_data<T>(path);
+		eps = eps_;
+		G = G_;
+		return *this;
+	}
+};
+
+// ---- asynchronous trajectory sink (K4, host half) -------------------------------------------
+// The integrator thread hands (time, snapshot ticket) pairs over; this thread waits for
+// the pinned copy, formats the row and releases the ring slot, so text formatting and
+// file I/O stay off the GPU's critical path.
+template <typename T>
+class TrajectoryWriter {
+   public:
+	TrajectoryWriter(nbody_ctx* ctx, std::ostream* out, std::size_t n)
+		: ctx_(ctx), out_(out), n_(n), th_([this] { run(); }) {}
+	~TrajectoryWriter() { finish(); }
+	// blocks while all ring slots are in flight (back-pressure)
+	void push(double time) {
+		{
+			std::unique_lock<std::mutex> lk(mu_);
+			cv_.wait(lk, [&] { return q_.size() < (std::size_t)NBODY_SNAPSHOT_SLOTS; });
+		}
+		uint64_t ticket = 0;
+		if (nbody_snapshot_async(ctx_, &ticket) != NBODY_OK) {
+			std::cout << "snapshot failed: " << nbody_last_error(ctx_) << std::endl;
+			return;
+		}
+		std::lock_guard<std::mutex> lk(mu_);
+		q_.push_back({time, ticket});
+		cv_.notify_all();
+	}
+	void finish() {
+		{
+			std::lock_guard<std::mutex> lk(mu_);
+			if (done_) return;
+			done_ = true;
+			cv_.notify_all();
+		}
+		th_.join();
+	}
+	double busy_seconds() const { return busy_; }
+
+   private:
+	struct Item { double time; uint64_t ticket; };
+	void run() {
+		for (;;) {
+			Item it;
+			{
+				std::unique_lock<std::mutex> lk(mu_);
+				cv_.wait(lk, [&] { return done_ || !q_.empty(); });
+				if (q_.empty()) return;
+				it = q_.front();
+			}
+			const void* p = nullptr;
+			if (nbody_snapshot_wait(ctx_, it.ticket, &p) == NBODY_OK) {
+				auto t0 = std::chrono::steady_clock::now();
+				write_positions_row(*out_, it.time, (const T*)p, n_);
+				busy_ += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+			}
+			nbody_snapshot_release(ctx_, it.ticket);
+			{
+				std::lock_guard<std::mutex> lk(mu_);
+				q_.pop_front();
+				cv_.notify_all();
+			}
+		}
+	}
+	nbody_ctx* ctx_;
+	std::ostream* out_;
+	std::size_t n_;
+	std::mutex mu_;
+	std::condition_variable cv_;
+	std::deque<Item> q_;
+	bool done_ = false;
+	double busy_ = 0;
+	std::thread th_;
+};
+
+struct RunOptions {
+	int scheme = NBODY_RK2;	 // the reference's scheme; NBODY_RK4 is the extension
+	int n_gpus = 1;
+	std::string flavour = "lab4";  // lab4: t_start row + 4-body header; lab5: N-body header, no t_start row
+	std::string traj_path;		   // "" = no trajectory (as for "4Body_random")
+	std::string timing_path;	   // "" = derive as the reference does
+	std::string final_state_path;
+	long out_every = 1;
+	long max_steps = 0;
+	long variant = -1;
+	bool report = false;
+};
+
+struct RunResult {
+	long steps = 0;
+	double wall_s = 0, gpu_ms = 0, writer_busy_s = 0;
+	double interactions = 0;
+	double e_kin0 = 0, e_pot0 = 0, e_kin1 = 0, e_pot1 = 0;
+};
+
+template <typename T>
+class Solver_N_body {
+   public:
+	T tol = T(1e-6);
+	bool notifications = false;
+	T timer = 0;
+	std::size_t iter = 0;
+	std::string file_name;
+	std::string output_folder = "../output/";
+	std::vector<Body<T>> final_state;
+	RunResult result;
+
+	Solver_N_body() = default;
+	Solver_N_body(T tol_, std::string output_folder_, std::string file_name_)
+		: tol(tol_), file_name(std::move(file_name_)), output_folder(std::move(output_folder_)) {}
+
+	// Counterpart of solve_parallel_MPI(sys, OS): one thread per GPU plays the MPI rank.
+	void solve_parallel_CUDA(ode_system<T>& sys, const RunOptions& opt, std::string OS = "PC") {
+		(void)OS;
+		if (notifications) std::cout << file_name << ": solving... \t";
+		const std::size_t n = sys.traj_init.size();
+		const int world = opt.n_gpus;
+		if ((std::size_t)world > n)	 // class_Solver_N_body.hpp:115-117
+			throw "The number of processes is greater than the problem dimension";
+		char uid[NBODY_NCCL_UID_BYTES] = {};
+		if (world > 1 && nbody_nccl_unique_id(uid) != NBODY_OK)
+			throw std::runtime_error(std::string("NCCL: ") + nbody_last_error(nullptr));
+		std::vector<std::string> errors(world);
+		std::vector<std::thread> ranks;
+		for (int r = 1; r < world; ++r)
+			ranks.emplace_back([&, r] { rank_main(sys, opt, r, world, uid, errors[r]); });
+		rank_main(sys, opt, 0, world, uid, errors[0]);
+		for (auto& t : ranks) t.join();
+		for (auto& e : errors)
+			if (!e.empty()) throw std::runtime_error(e);
+		if (notifications) std::cout << "  Done!\n";
+	}
+
+   private:
+	void rank_main(ode_system<T>& sys, const RunOptions& opt, int rank, int world,
+				   const char* uid, std::string& error) {
+		const std::size_t n = sys.traj_init.size();
+		nbody_ctx* ctx = nullptr;
+		const int prec = std::is_same<T, double>::value ? 64 : 32;
+		if (nbody_create(&ctx, n, prec, rank, rank, world, world > 1 ? uid : nullptr) != NBODY_OK) {
+			error = std::string("nbody_create: ") + nbody_last_error(nullptr);
+			return;
+		}
+		auto fail = [&](const char* what) {
+			error = std::string(what) + ": " + nbody_last_error(ctx);
+			nbody_destroy(ctx);
+		};
+		if (nbody_set_params(ctx, (double)sys.G, (double)sys.eps)) return fail("set_params");
+		if (opt.variant >= 0 && nbody_set_option(ctx, "variant", opt.variant)) return fail("variant");
+		if (nbody_upload_aos(ctx, sys.traj_init.data())) return fail("upload");
+
+		std::ofstream traj;
+		const bool writes = rank == 0 && !opt.traj_path.empty();
+		if (writes) {
+			traj.open(opt.traj_path);
+			if (!traj.is_open()) std::cout << "Could not open file for writing" << std::endl;
+			if (opt.flavour == "lab5") traj << lab5_header(n);
+			else {
+				traj << lab4_header();
+				write_bodies_coords(traj, (double)sys.t_start, sys.traj_init);	// ode_RK2_MPI.hpp:63
+			}
+		}
+		if (opt.report && nbody_energy(ctx, &result_slot(rank).e_kin0, &result_slot(rank).e_pot0))
+			return fail("energy");
+
+		RunResult& res = result_slot(rank);
+		{
+			std::unique_ptr<TrajectoryWriter<T>> writer;
+			if (writes) writer.reset(new TrajectoryWriter<T>(ctx, &traj, n));
+			const auto w0 = std::chrono::steady_clock::now();
+			// The reference's loop, in T: ode_RK2_MPI.hpp:65,72,98-99
+			T t = sys.t_start + sys.tau;
+			long steps = 0;
+			while (true) {
+				if (nbody_step(ctx, opt.scheme, (double)sys.tau, 1)) return fail("step");
+				nbody_timing tm;
+				++steps;
+				if (writer && (steps % opt.out_every == 0)) writer->push((double)t);
+				if (opt.max_steps > 0 && steps >= opt.max_steps) break;
+				if (t > sys.t_final) break;
+				t += sys.tau;
+				(void)tm;
+			}
+			if (nbody_sync(ctx)) return fail("sync");
+			if (writer) {
+				writer->finish();
+				res.writer_busy_s = writer->busy_seconds();
+			}
+			res.wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
+			res.steps = steps;
+			const int stages = opt.scheme == NBODY_RK2 ? 2 : 4;
+			res.interactions = (double)stages * (double)n * (double)n * (double)steps;
+		}
+		if (opt.report && nbody_energy(ctx, &res.e_kin1, &res.e_pot1)) return fail("energy");
+		std::vector<Body<T>> fin(n);
+		if (nbody_download_aos(ctx, fin.data())) return fail("download");
+		if (rank == 0) {
+			final_state.swap(fin);
+			timer = (T)res.wall_s;
+			iter = (std::size_t)res.steps;
+			result = res;
+			if (!opt.final_state_path.empty()) write_input_format(opt.final_state_path, final_state);
+			write_timing_csv(sys, opt, world);
+		}
+		nbody_destroy(ctx);
+	}
+
+	RunResult& result_slot(int rank) {
+		static thread_local RunResult other;
+		return rank == 0 ? result : other;
+	}
+
+	void write_timing_csv(const ode_system<T>& sys, const RunOptions& opt, int world) {
+		std::string path = opt.timing_path;
+		if (path.empty())  // class_Solver_N_body.hpp:98-108
+			path = output_folder + "/output_" + sys.name + "_" + std::to_string(sys.tau) + "_np_" +
+				   std::to_string(world) + ".csv";
+		std::ofstream out(path);
+		if (!out.is_open()) return;
+		if (opt.flavour == "lab5") {  // N_body.cu:226,397-399
+			const int n_steps = (int)((sys.t_final - sys.t_start) / sys.tau);
+			out << "type;n_bodies;n_steps;block_size;time_taken;avg_exec_time\n";
+			out << (std::is_same<T, double>::value ? "double" : "float") << ";"
+				<< sys.traj_init.size() << ";" << n_steps << ";" << 128 << ";" << result.wall_s
+				<< ";" << result.wall_s / (n_steps > 0 ? n_steps : 1) << "\n";
+		} else {  // class_Solver_N_body.hpp:110-111,199-202
+			out << "size;t_start;t_finish;tau;time_steps;num_procs;time_taken;avg_time_for_step\n";
+			out << sys.traj_init.size() << ";" << sys.t_start << ";" << sys.t_final << ";" << sys.tau
+				<< ";" << sys.n_time_steps << ";" << world << ";" << timer << ";"
+				<< timer / sys.n_time_steps << "\n";
+		}
+	}
+};
+
+// lab_5's entry point with its own signature (N_body.cu:208-210): SoA host vectors in,
+// timing CSV at `path`, trajectory CSV at `path_1` (lab_5 flavour).
+template <typename T>
+void ode_RK2_CUDA(const std::vector<T>& m, const std::vector<Vec4<T>>& r,
+				  const std::vector<Vec4<T>>& v, T t_start, T t_final, T tau,
+				  std::string path = "", std::string path_1 = "", T eps = T(1e-6),
+				  T G = T(6.67e-11)) {
+	ode_system<T> sys;
+	sys.name = "lab5";
+	sys.t_start = t_start;
+	sys.t_final = t_final;
+	sys.tau = tau;
+	sys.n_time_steps = (int)((t_final - t_start) / tau);
+	sys.eps = eps;
+	sys.G = G;
+	sys.traj_init.resize(m.size());
+	for (std::size_t i = 0; i < m.size(); ++i) {
+		sys.traj_init[i].m = m[i];
+		sys.traj_init[i].r = {r[i].x, r[i].y, r[i].z};
+		sys.traj_init[i].v = {v[i].x, v[i].y, v[i].z};
+	}
+	RunOptions opt;
+	opt.flavour = "lab5";
+	opt.scheme = NBODY_RK2;
+	opt.timing_path = path.empty() ? "/dev/null" : path;
+	opt.traj_path = path_1;
+	Solver_N_body<T> solver;
+	solver.solve_parallel_CUDA(sys, opt);
+}
+
+}  // namespace nbody_host

@@ -1,0 +1,136 @@
+// nbody_main.cpp -- C++ host driver (the lab's `N_body_server`, B200 edition).
+//
+// Mirrors what the reference's two mains do by editing source
+// (lab_4_N_body_MPI/src/N_body.cpp:38-87, lab_5_N_body_CUDA/src/N_body.cu:408-497),
+// as run-time flags with the reference's parameter names and defaults:
+//   --system default_test|random   ode_system_default_test / ode_system_random_data
+//   --input PATH                    body file "N" + "m x y z vx vy vz" per line
+//   --tau --t-start --t-final --eps --G
+//   --precision 64|32   --scheme rk2|rk4   --gpus P   --flavour lab4|lab5
+//   --traj-out PATH  --timing-out PATH  --final-state PATH  --out-every K  --max-steps K
+//   --output-folder DIR (where the reference-named CSVs go)  --report (energy, rates)
+// All computation happens behind the C ABI (include/nbody_b200.h); no CPU fallback.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <map>
+#include <stdexcept>
+#include <string>
+
+#include "nbody_host.hpp"
+
+using namespace nbody_host;
+
+namespace {
+struct Args {
+	std::map<std::string, std::string> kv;
+	bool has(const std::string& k) const { return kv.count(k) != 0; }
+	std::string str(const std::string& k, const std::string& d) const {
+		auto it = kv.find(k);
+		return it == kv.end() ? d : it->second;
+	}
+	double num(const std::string& k, double d) const {
+		auto it = kv.find(k);
+		return it == kv.end() ? d : std::strtod(it->second.c_str(), nullptr);
+	}
+};
+
+void usage() {
+	std::puts(
+		"nbody_b200 --input FILE [--system default_test|random] [--tau 0.1] [--t-start 0]\n"
+		"           [--t-final 20|1] [--eps 1e-6] [--G 6.67e-11] [--precision 64|32]\n"
+		"           [--scheme rk2|rk4] [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
+		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
+		"           [--output-folder ../output] [--variant -1] [--report]");
+}
+
+template <typename T>
+int run(const Args& a) {
+	ode_system<T> sys;
+	const std::string system = a.str("system", "random");
+	const T tau = (T)a.num("tau", 0.1);
+	const T eps = (T)a.num("eps", 1e-6);
+	const T G = (T)a.num("G", 6.67e-11);
+	try {
+		if (system == "default_test")
+			sys.ode_system_default_test(tau, eps, G,
+										a.str("input", "./include/N_body/N_body_config/4body.txt"));
+		else
+			sys.ode_system_random_data(0, tau, eps, G, a.str("input", "../output/rand_bodies.txt"));
+	} catch (int code) {
+		return code;  // the reference lets `throw 1` terminate the program
+	}
+	if (a.has("t-start")) sys.t_start = (T)a.num("t-start", 0);
+	if (a.has("t-final")) sys.t_final = (T)a.num("t-final", 1);
+	sys.n_time_steps = (int)((sys.t_final - sys.t_start) / sys.tau);
+	sys.N_bodies = (int)sys.traj_init.size();
+
+	RunOptions opt;
+	opt.scheme = a.str("scheme", "rk2") == "rk4" ? NBODY_RK4 : NBODY_RK2;
+	opt.n_gpus = (int)a.num("gpus", 1);
+	opt.flavour = a.str("flavour", "lab4");
+	opt.traj_path = a.str("traj-out", "");
+	opt.timing_path = a.str("timing-out", "");
+	opt.final_state_path = a.str("final-state", "");
+	opt.out_every = (long)a.num("out-every", 1);
+	if (opt.out_every < 1) opt.out_every = 1;
+	opt.max_steps = (long)a.num("max-steps", 0);
+	opt.variant = (long)a.num("variant", -1);
+	opt.report = a.has("report");
+
+	Solver_N_body<T> solver;
+	solver.output_folder = a.str("output-folder", "../output");
+	solver.notifications = a.has("notifications");
+	// the reference derives the trajectory name for the 4-body test
+	// (class_Solver_N_body.hpp:185-187)
+	if (opt.traj_path.empty() && sys.name == "4Body_test" && !a.has("no-traj"))
+		opt.traj_path = solver.output_folder + "/results_" + std::to_string(sys.tau) + ".csv";
+	try {
+		solver.solve_parallel_CUDA(sys, opt);
+	} catch (const char* msg) {
+		std::cerr << msg << std::endl;
+		return 2;
+	} catch (const std::exception& e) {
+		std::cerr << "error: " << e.what() << std::endl;
+		return 3;
+	}
+	if (opt.report) {
+		const RunResult& r = solver.result;
+		const double e0 = r.e_kin0 + r.e_pot0, e1 = r.e_kin1 + r.e_pot1;
+		std::printf(
+			"{\"n\": %zu, \"precision\": %d, \"scheme\": \"%s\", \"gpus\": %d, \"steps\": %ld, "
+			"\"wall_s\": %.6f, \"G_interactions_per_s\": %.3f, \"writer_busy_s\": %.6f, "
+			"\"energy0\": %.17g, \"energy1\": %.17g, \"energy_drift\": %.3e}\n",
+			sys.traj_init.size(), (int)(8 * sizeof(T)), opt.scheme == NBODY_RK4 ? "rk4" : "rk2",
+			opt.n_gpus, r.steps, r.wall_s, r.interactions / r.wall_s / 1e9, r.writer_busy_s, e0, e1,
+			e0 != 0 ? std::fabs(e1 - e0) / std::fabs(e0) : 0.0);
+	}
+	return 0;
+}
+}  // namespace
+
+int main(int argc, char** argv) {
+	Args a;
+	for (int i = 1; i < argc; ++i) {
+		std::string k = argv[i];
+		if (k == "-h" || k == "--help") {
+			usage();
+			return 0;
+		}
+		if (k.rfind("--", 0) != 0) {
+			std::cerr << "unexpected argument " << k << std::endl;
+			usage();
+			return 64;
+		}
+		k = k.substr(2);
+		if (i + 1 < argc && std::strncmp(argv[i + 1], "--", 2) != 0) a.kv[k] = argv[++i];
+		else a.kv[k] = "1";
+	}
+	const int prec = (int)a.num("precision", 64);
+	if (prec == 64) return run<double>(a);
+	if (prec == 32) return run<float>(a);
+	std::cerr << "--precision must be 64 or 32" << std::endl;
+	return 64;
+}
