@@ -67,6 +67,15 @@ int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank,
 				 const void* nccl_uid);
 void nbody_destroy(nbody_ctx* ctx);
 
+/* The i-row partition nbody_create uses, as pure host arithmetic (no GPU needed):
+ * rank r owns global rows [begin,end); all ranks exchange equal blocks of block_rows
+ * rows (padded with zero-mass bodies that contribute exactly 0), block_rows * world >= n.
+ * Counterpart of counts[]/offsets[] in lab_4 .../class_Solver_N_body.hpp:119-130 (which
+ * gives the remainder to the last rank; NCCL all-gather wants equal counts instead).
+ * Returns NBODY_ERR_ARG where the reference throws (world > n). */
+int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
+					size_t* block_rows);
+
 /* G and eps captured by the RHS lambda (lab_4 .../struct_ode_system.hpp:34-36,53;
  * lab_5 N_body.cu:22,30).  Defaults 6.67e-11 and 1e-6. */
 int nbody_set_params(nbody_ctx* ctx, double G, double eps);

@@ -58,6 +58,8 @@ def lib() -> C.CDLL:
     L.nbody_create.argtypes = [C.POINTER(vp), sz, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     L.nbody_destroy.argtypes = [vp]
     L.nbody_destroy.restype = None
+    L.nbody_partition.argtypes = [sz, C.c_int, C.c_int, C.POINTER(sz), C.POINTER(sz),
+                                  C.POINTER(sz)]
     L.nbody_set_params.argtypes = [vp, C.c_double, C.c_double]
     L.nbody_set_option.argtypes = [vp, C.c_char_p, C.c_long]
     L.nbody_owned_range.argtypes = [vp, C.POINTER(sz), C.POINTER(sz)]
@@ -87,6 +89,14 @@ def declared_symbols() -> list[str]:
     txt = open(HEADER_PATH).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     return sorted(set(re.findall(r"\b(nbody_[a-z0-9_]+)\s*\(", txt)))
+
+
+def partition(n: int, world: int, rank: int):
+    """(begin, end, block_rows) of rank's owned rows; ValueError where the reference throws."""
+    b, e, blk = C.c_size_t(), C.c_size_t(), C.c_size_t()
+    if lib().nbody_partition(n, world, rank, C.byref(b), C.byref(e), C.byref(blk)):
+        raise ValueError(lib().nbody_last_error(None).decode())
+    return b.value, e.value, blk.value
 
 
 def nccl_unique_id() -> bytes:

@@ -242,7 +242,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
 		const unsigned row0 = itile * (THREADS * I) + tid;
 #pragma unroll
 		for (int k = 0; k < I; ++k) {
-			const vec4 b = pos[(size_t)p.own0 + row0 + k * THREADS];
+			// the last i-tile may reach past the owned block: clamp the load, drop the store
+			const unsigned row = min(row0 + k * THREADS, p.own_pad - 1u);
+			const vec4 b = pos[(size_t)p.own0 + row];
 			xi[k] = b.x;
 			yi[k] = b.y;
 			zi[k] = b.z;
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			o.y = acc.y[k];
 			o.z = acc.z[k];
 			o.w = T(0);
-			out[row0 + k * THREADS] = o;
+			if (row0 + k * THREADS < p.own_pad) out[row0 + k * THREADS] = o;
 		}
 		if (tid == 0) *next_unit_s = next_ticket;
 		__syncthreads();

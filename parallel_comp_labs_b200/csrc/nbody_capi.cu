@@ -117,7 +117,7 @@ const Variant g_var32[] = {
 };
 constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
 constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
-constexpr unsigned PAD_UNIT = 2048;	 // multiple of every variant's THREADS*I and of TJ
+constexpr unsigned PAD_UNIT = 256;	 // == TJ: per-rank blocks are whole j-tiles
 constexpr unsigned MAX_SLICES = 64;
 }  // namespace
 
@@ -482,6 +482,22 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 	return NBODY_OK;
 }
 
+int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
+					size_t* block_rows) {
+	if (n == 0 || world < 1 || rank < 0 || rank >= world || !begin || !end || !block_rows)
+		return fail(nullptr, NBODY_ERR_ARG, "nbody_partition: bad argument");
+	if ((size_t)world > n)	// class_Solver_N_body.hpp:115-117
+		return fail(nullptr, NBODY_ERR_ARG,
+					"The number of processes is greater than the problem dimension");
+	const size_t per = (n + world - 1) / world;
+	const size_t blk = (per + PAD_UNIT - 1) / PAD_UNIT * PAD_UNIT;
+	const size_t b = std::min(n, blk * (size_t)rank);
+	*begin = b;
+	*end = std::min(n, blk * (size_t)(rank + 1));
+	*block_rows = blk;
+	return NBODY_OK;
+}
+
 int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank, int world,
 				 const void* nccl_uid) {
 	if (!out) return fail(nullptr, NBODY_ERR_ARG, "nbody_create: null output");
@@ -503,11 +519,12 @@ int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank,
 	ctx->device = device;
 	ctx->rank = rank;
 	ctx->world = world;
-	const size_t per = (n + world - 1) / world;
-	ctx->own_pad = (unsigned)((per + PAD_UNIT - 1) / PAD_UNIT * PAD_UNIT);
+	size_t pb = 0, pe = 0, blk = 0;
+	nbody_partition(n, world, rank, &pb, &pe, &blk);
+	ctx->own_pad = (unsigned)blk;
 	ctx->n_pad = ctx->own_pad * (unsigned)world;
 	ctx->own0 = ctx->own_pad * (unsigned)rank;
-	ctx->own_real = ctx->own0 >= n ? 0u : (unsigned)std::min<size_t>(ctx->own_pad, n - ctx->own0);
+	ctx->own_real = (unsigned)(pe - pb);
 	int rc = create_impl(ctx, nccl_uid);
 	if (rc != NBODY_OK) {
 		std::string e = ctx->err;

@@ -1,0 +1,78 @@
+"""The C++ host driver binary (parallel_comp_labs_b200/bin/nbody_b200) end to end: reads the
+lab's body file, writes the lab's CSVs (both flavours), final-state dump is restartable."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from parallel_comp_labs_b200 import generators, lab
+
+pytestmark = pytest.mark.gpu
+EXE = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+IN4 = os.path.join(ROOT, "tests", "golden", "_4body.txt")
+
+
+def run(*args):
+    r = subprocess.run([EXE, *map(str, args)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr + r.stdout
+    return r.stdout
+
+
+def parse(path):
+    lines = open(path).read().splitlines()
+    return lines[0], np.array([[float(x) for x in l.split(";")[:-1]] for l in lines[1:]])
+
+
+def test_lab4_flavour_4body(golden, tmp_path):
+    run("--system", "default_test", "--input", IN4, "--tau", 0.1, "--output-folder", tmp_path)
+    header, rows = parse(tmp_path / "results_0.100000.csv")
+    assert header + "\n" == lab.LAB4_HEADER
+    ref = golden["ref_rk2_4body_0100"]
+    assert rows.shape == ref.shape == (201, 13)
+    assert np.array_equal(rows[:, 0], ref[:, 0])
+    assert np.abs(rows - ref).max() < 1e-10
+    raw = open(tmp_path / "results_0.100000.csv", "rb").read().splitlines()
+    assert raw[1] == bytes(golden["ref_row_bytes"]).splitlines()[0].replace(
+        b"3.0000000000000004e-01", b"0.0000000000000000e+00")        # t_start row, byte for byte
+    t = open(tmp_path / "output_4Body_test_0.100000_np_1.csv").read().splitlines()
+    assert t[0] == "size;t_start;t_finish;tau;time_steps;num_procs;time_taken;avg_time_for_step"
+    assert t[1].startswith("4;0;20;0.1;200;1;")
+
+
+def test_lab5_flavour_fp32(golden, tmp_path):
+    run("--system", "default_test", "--input", IN4, "--precision", 32, "--flavour", "lab5",
+        "--traj-out", tmp_path / "res4body_async.csv", "--timing-out", tmp_path / "t.csv")
+    header, rows = parse(tmp_path / "res4body_async.csv")
+    assert header + "\n" == lab.lab5_header(4)
+    ref = golden["lab5_res4body_async"]
+    assert rows.shape == ref.shape == (200, 13)                       # no t_start row
+    assert np.array_equal(rows[:, 0], ref[:, 0])                      # time printed as float
+    assert np.abs(rows - ref).max() < 2e-4
+    t = open(tmp_path / "t.csv").read().splitlines()
+    assert t[0] == "type;n_bodies;n_steps;block_size;time_taken;avg_exec_time"
+    assert t[1].startswith("float;4;200;")
+
+
+def test_random_system_restart_and_report(oracle, tmp_path):
+    b = generators.uniform_bodies(1500, seed=21)
+    inp = tmp_path / "rand_bodies.txt"
+    with open(inp, "w") as f:
+        f.write("1500\n")
+        for r in b:
+            f.write("\t".join("%.17g" % x for x in r) + "\n")
+    out = run("--input", inp, "--scheme", "rk4", "--tau", 0.1, "--t-final", 0.35,
+              "--final-state", tmp_path / "final.txt", "--timing-out", tmp_path / "t.csv",
+              "--traj-out", tmp_path / "traj.csv", "--out-every", 2, "--report")
+    rep = json.loads(out.strip().splitlines()[-1])
+    steps = oracle.step_count(0.0, 0.35, 0.1)
+    assert rep["steps"] == steps == 4 and rep["n"] == 1500
+    fin = lab.read_data(str(tmp_path / "final.txt"))
+    want, _ = oracle.rk4(b, 0.1, 0.0, 0.35, rows=False, threads=4)
+    assert np.abs(fin[:, 1:4] - want[:, 1:4]).max() / np.abs(want[:, 1:4]).max() < 1e-10
+    assert np.abs(fin[:, 4:7] - want[:, 4:7]).max() / np.abs(want[:, 4:7]).max() < 1e-10
+    header, rows = parse(tmp_path / "traj.csv")
+    assert rows.shape == (1 + 2, 1 + 3 * 1500)                        # t_start row + every 2nd step
+    assert rep["energy_drift"] < 1e-3

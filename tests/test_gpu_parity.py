@@ -1,0 +1,326 @@
+"""Parity of the CUDA path (through the C ABI, libnbody_b200.so) against the oracle and the
+committed golden fixtures.  Tolerances (BASELINE.json north_star): positions and velocities
+within 1e-10 relative for FP64 and 1e-4 for FP32 over a short horizon; the RHS itself is held
+to 1e-12 (FP64).  "Relative" = inf-norm of the difference over the inf-norm of the reference
+quantity; velocities are compared through their INCREMENTS v(t)-v(0) as well, because on the
+bundled random bodies free streaming hides force errors (SURVEY.md 4 warning)."""
+import numpy as np
+import pytest
+
+from conftest import rel_inf
+from parallel_comp_labs_b200 import capi, generators, lab
+
+pytestmark = pytest.mark.gpu
+
+TOL64_RHS, TOL64_TRAJ, TOL32 = 1e-12, 1e-10, 1e-4
+
+
+def gpu_rhs(bodies, prec=64, eps=1e-6, G=6.67e-11, variant=-1, slices=0):
+    with capi.Context(bodies.shape[0], prec) as ctx:
+        ctx.set_params(G, eps)
+        ctx.set_option("variant", variant)
+        ctx.set_option("slices", slices)
+        ctx.upload_aos(bodies)
+        return ctx.rhs().astype(np.float64)
+
+
+def gpu_run(bodies, scheme, tau, steps, prec=64, eps=1e-6, G=6.67e-11, graph=0):
+    with capi.Context(bodies.shape[0], prec) as ctx:
+        ctx.set_params(G, eps)
+        ctx.set_option("use_graph", graph)
+        ctx.upload_aos(bodies)
+        ctx.step(scheme, tau, steps, sync=True)
+        return ctx.download_aos().astype(np.float64)
+
+
+def check_state(got, want, init, tol):
+    assert np.array_equal(got[:, 0], want[:, 0])                      # masses untouched
+    assert rel_inf(got[:, 1:4], want[:, 1:4]) < tol
+    assert rel_inf(got[:, 4:7], want[:, 4:7]) < tol
+    dv_w = want[:, 4:7] - init[:, 4:7]
+    if np.abs(dv_w).max() > 0:
+        assert rel_inf(got[:, 4:7] - init[:, 4:7], dv_w) < max(tol, 1e-9 if tol < 1e-6 else tol)
+
+
+# ------------------------------------------------------------------ RHS
+def test_rhs_golden_fixtures(golden, rand10k):
+    assert rel_inf(gpu_rhs(golden["body4"]), golden["ref_rhs_body4"]) < TOL64_RHS
+    assert rel_inf(gpu_rhs(golden["rand512"]), golden["ref_rhs_rand512"]) < TOL64_RHS
+    uni = generators.uniform_bodies(777, seed=0x5EED0001)
+    assert rel_inf(gpu_rhs(uni), golden["ref_rhs_uniform777"]) < TOL64_RHS
+    plu = golden["plummer1000_in"]       # has a pair inside the clamp radius and a coincident pair
+    got = gpu_rhs(plu, eps=1e-3)
+    assert np.all(np.isfinite(got))
+    assert rel_inf(got, golden["ref_rhs_plummer1000_eps1e-3"]) < TOL64_RHS
+    # the clamped pair itself, relative to its own magnitude
+    for i in (10, 11, 20, 21):
+        assert rel_inf(got[i], golden["ref_rhs_plummer1000_eps1e-3"][i]) < 1e-11
+    bodies, rows32, last8 = rand10k      # the reference's own 10 000-body input
+    got = gpu_rhs(bodies)
+    scale = np.abs(rows32).max()
+    assert np.abs(got[:32] - rows32).max() / scale < TOL64_RHS
+    assert np.abs(got[9992:] - last8).max() / scale < TOL64_RHS
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 255, 256, 257, 511, 513, 1000, 4097])
+def test_rhs_ragged_sizes_vs_oracle(oracle, n):
+    bodies = generators.uniform_bodies(n, seed=100 + n)
+    want = oracle.rhs(bodies, threads=4)[:, 4:7]
+    got = gpu_rhs(bodies)
+    assert got.shape == (n, 3) and np.all(np.isfinite(got))
+    if n == 1:
+        assert np.all(got == 0) and np.all(want == 0)     # only the self term: exactly 0
+    else:
+        assert rel_inf(got, want) < TOL64_RHS
+
+
+def test_rhs_all_variants_and_slicings(oracle):
+    bodies = generators.plummer_bodies(3000, seed=5)
+    bodies[7, 1:4] = bodies[8, 1:4] + 1e-5
+    want = oracle.rhs(bodies, eps=1e-3, threads=8)[:, 4:7]
+    var = 0
+    while True:
+        try:
+            got = gpu_rhs(bodies, eps=1e-3, variant=var)
+        except capi.NBodyError:
+            break
+        assert rel_inf(got, want) < TOL64_RHS, var
+        var += 1
+    assert var >= 4
+    for s in (1, 2, 5, 12):
+        assert rel_inf(gpu_rhs(bodies, eps=1e-3, slices=s), want) < TOL64_RHS
+    v32 = 0
+    while True:
+        try:
+            got = gpu_rhs(bodies, prec=32, eps=1e-3, variant=v32)
+        except capi.NBodyError:
+            break
+        # the planted pair sits 1e-5 apart: in FP32 its separation itself is rounded, so the
+        # two rows it dominates are excluded from the FP32 tolerance
+        mask = np.ones(3000, bool)
+        mask[[7, 8]] = False
+        assert np.abs(got[mask] - want[mask]).max() / np.abs(want[mask]).max() < TOL32, v32
+        v32 += 1
+    assert v32 >= 3
+
+
+def test_rhs_edge_cases(oracle):
+    b = generators.uniform_bodies(600, seed=3)
+    b[5, 0] = 0.0                       # zero-mass body: feels forces, exerts none
+    b[40, 1:4] = b[41, 1:4]             # coincident pair: clamp -> exactly zero pair term
+    b[100, 1:4] = b[101, 1:4] + 3e-7    # inside eps=1e-6
+    want = oracle.rhs(b)[:, 4:7]
+    got = gpu_rhs(b)
+    assert np.all(np.isfinite(got)) and rel_inf(got, want) < TOL64_RHS
+    for i in (100, 101):
+        assert rel_inf(got[i], want[i]) < 1e-11
+    # linearity in G and in the masses (size-independent property)
+    g2 = gpu_rhs(b, G=2 * 6.67e-11)
+    assert rel_inf(g2, 2 * got) < 1e-15
+    b2 = b.copy()
+    b2[:, 0] *= 4.0
+    assert rel_inf(gpu_rhs(b2), 4 * got) < 1e-15
+    # large eps: everything inside the clamp radius -> a_i = -G sum m_j (r_i-r_j)/eps^3
+    got = gpu_rhs(b, eps=1e4)
+    want = oracle.rhs(b, eps=1e4)[:, 4:7]
+    assert rel_inf(got, want) < TOL64_RHS
+
+
+def test_rhs_large_n_row_subsample(oracle):
+    """N = 262 144 Plummer: full parity is infeasible on CPU; the oracle evaluates 48 rows
+    against all N (exactly the begin,end API).  Plus Newton's third law: sum m_i a_i = 0."""
+    n = 262144
+    bodies = generators.plummer_bodies(n, seed=0x5EED0003)
+    got = gpu_rhs(bodies, eps=1e-3)
+    scale = np.abs(got).max()
+    for begin in (0, 131072 - 8, n - 16):
+        want = oracle.rhs(bodies, begin, begin + 16, eps=1e-3, threads=8)[begin:begin + 16, 4:7]
+        assert np.abs(got[begin:begin + 16] - want).max() / np.abs(want).max() < TOL64_RHS
+    mom = (bodies[:, 0:1] * got).sum(axis=0)
+    assert np.abs(mom).max() / (bodies[:, 0].sum() * scale) < 1e-12
+
+
+# ------------------------------------------------------------------ integrators
+@pytest.mark.parametrize("tau,key,stride", [(0.1, "0100", 1), (0.05, "0050", 8), (0.025, "0025", 8)])
+def test_rk2_4body_every_row_vs_reference(golden, tau, key, stride):
+    """The reference's own RK2 trajectory of its 4-body problem, every stored row."""
+    b4 = golden["body4"]
+    ref = golden[f"ref_rk2_4body_{key}"]
+    nsteps = lab.step_count(0.0, 20.0, tau)
+    assert nsteps + 1 == int(golden[f"ref_rk2_4body_{key}_nrows"][0])
+    rows = [np.concatenate([[0.0], b4[:, 1:4].ravel()])]
+    with capi.Context(4, 64) as ctx:
+        ctx.upload_aos(b4)
+        t = 0.0 + tau
+        for k in range(nsteps):
+            ctx.step(capi.NBODY_RK2, tau, 1)
+            rows.append(np.concatenate([[t], ctx.snapshot().ravel()]))
+            t += tau
+    rows = np.array(rows)[::stride]
+    assert rows.shape == ref.shape
+    assert np.array_equal(rows[:, 0], ref[:, 0])                        # time column, bit for bit
+    assert np.abs(rows[:, 1:] - ref[:, 1:]).max() < TOL64_TRAJ          # |r| ~ 1
+    assert np.all(rows[:, 3::3] == 0)                                   # z stays exactly 0
+
+
+def test_rk4_vs_oracle_and_golden(oracle, golden):
+    b4 = golden["body4"]
+    got = gpu_run(b4, capi.NBODY_RK4, 0.1, 200, graph=1)
+    check_state(got, golden["ref_rk4_4body_0100_final"], b4, TOL64_TRAJ)
+    uni = generators.uniform_bodies(777, seed=0x5EED0001)
+    check_state(gpu_run(uni, capi.NBODY_RK4, 0.1, 3), golden["ref_rk4_uniform777_3steps"], uni,
+                TOL64_TRAJ)
+    plu = golden["plummer1000_in"]
+    check_state(gpu_run(plu, capi.NBODY_RK4, 1e-3, 3, eps=1e-3),
+                golden["ref_rk4_plummer1000_3steps"], plu, TOL64_TRAJ)
+
+
+def test_rk2_rand512_vs_reference_rows(golden):
+    b = golden["rand512"]
+    with capi.Context(512, 64) as ctx:
+        ctx.upload_aos(b)
+        for k, idx in ((1, 0), (6, 1), (11, 2)):
+            ctx.step(capi.NBODY_RK2, 0.1, k - (0 if idx == 0 else (1, 6)[idx - 1]), sync=True)
+            pos = ctx.snapshot().ravel()
+            ref = golden["ref_rk2_rand512_rows"][idx, 1:]
+            assert np.abs(pos - ref).max() / np.abs(ref).max() < TOL64_TRAJ
+
+
+def test_rk2_rk4_uniform20k_config(oracle):
+    """BASELINE.json configs[1] (uniform N=20k FP64): 2 steps against the oracle."""
+    b = generators.uniform_bodies(20000, seed=0x5EED0001)
+    want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, max_steps=2, rows=False, threads=oracle.max_threads())
+    check_state(gpu_run(b, capi.NBODY_RK4, 0.1, 2), want, b, TOL64_TRAJ)
+
+
+def test_known_answer_order_of_accuracy(golden):
+    """Against the reference's accurate solution traj{1..4}.csv."""
+    truth = np.stack([golden[f"traj{k}"][:, 1:4] for k in (1, 2, 3, 4)], axis=1)
+    errs = {}
+    for scheme, tau, every in ((2, 0.1, 1), (2, 0.05, 2), (2, 0.025, 4), (4, 0.1, 1)):
+        with capi.Context(4, 64) as ctx:
+            ctx.upload_aos(golden["body4"])
+            pos = []
+            for k in range(200):
+                ctx.step(scheme, tau, every)
+                pos.append(ctx.snapshot())
+        errs[(scheme, tau)] = np.abs(np.array(pos) - truth[1:]).max()
+    assert abs(errs[(2, 0.1)] - 4.0853e-2) < 5e-6
+    assert abs(errs[(2, 0.05)] - 1.0966e-2) < 5e-6
+    assert abs(errs[(2, 0.025)] - 2.8310e-3) < 5e-6
+    assert abs(errs[(4, 0.1)] - 1.2157e-5) < 5e-8
+
+
+def test_graph_replay_equals_plain_launches(golden):
+    b = generators.uniform_bodies(1500, seed=8)
+    a = gpu_run(b, capi.NBODY_RK4, 0.05, 6, graph=0)
+    c = gpu_run(b, capi.NBODY_RK4, 0.05, 6, graph=1)
+    assert np.array_equal(a, c)
+
+
+def test_determinism():
+    b = generators.plummer_bodies(5000, seed=2)
+    a = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
+    c = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
+    assert np.array_equal(a, c)      # dynamic unit scheduling, fixed-order slice reduction
+
+
+# ------------------------------------------------------------------ FP32
+def test_fp32_path(oracle, golden):
+    b4 = golden["body4"]
+    # lab_5's committed FP32 GPU trajectory, through lab_5's own entry point and SoA layout
+    ref = golden["lab5_res4body_async"]
+    r4 = np.zeros((4, 4), np.float32)
+    v4 = np.zeros((4, 4), np.float32)
+    r4[:, :3], v4[:, :3] = b4[:, 1:4], b4[:, 4:7]
+    with capi.Context(4, 32) as ctx:
+        ctx.upload_soa(b4[:, 0].astype(np.float32), r4, v4)
+        rows = []
+        for k in range(200):
+            ctx.step(capi.NBODY_RK2, 0.1, 1)
+            rows.append(ctx.snapshot().ravel())
+    rows = np.array(rows, dtype=np.float64)
+    assert np.abs(rows[0] - ref[0, 1:]).max() < 2e-7
+    assert np.abs(rows - ref[:, 1:]).max() < TOL32 * 2
+    # FP32 vs the FP64 oracle on a random system, 5 steps
+    b = generators.uniform_bodies(2000, seed=4)
+    want, _ = oracle.rk2(b, 0.1, 0.0, 1.0, max_steps=5, rows=False, threads=8)
+    got = gpu_run(b, capi.NBODY_RK2, 0.1, 5, prec=32)
+    assert rel_inf(got[:, 1:4], want[:, 1:4]) < TOL32
+    assert rel_inf(got[:, 4:7], want[:, 4:7]) < TOL32
+    a32 = gpu_rhs(b, prec=32)
+    assert rel_inf(a32, oracle.rhs(b, threads=8)[:, 4:7]) < TOL32
+
+
+# ------------------------------------------------------------------ boundary behaviour
+def test_soa_upload_equals_aos(golden):
+    b = generators.uniform_bodies(900, seed=6)
+    r4 = np.zeros((900, 4))
+    v4 = np.zeros((900, 4))
+    r4[:, :3], v4[:, :3] = b[:, 1:4], b[:, 4:7]
+    r4[:, 3] = 123.0                                   # T3.w is ignored
+    with capi.Context(900, 64) as ctx:
+        ctx.upload_soa(b[:, 0], r4, v4)
+        ctx.step(capi.NBODY_RK2, 0.1, 2, sync=True)
+        a = ctx.download_aos()
+    assert np.array_equal(a, gpu_run(b, capi.NBODY_RK2, 0.1, 2))
+
+
+def test_snapshot_ring_and_errors():
+    b = generators.uniform_bodies(300, seed=9)
+    with capi.Context(300, 64) as ctx:
+        with pytest.raises(capi.NBodyError):
+            ctx.step(capi.NBODY_RK2, 0.1, 1)          # before upload
+        ctx.upload_aos(b)
+        with pytest.raises(capi.NBodyError):
+            ctx.step(3, 0.1, 1)                        # unknown scheme
+        tickets = [ctx.snapshot_async() for _ in range(capi.SNAPSHOT_SLOTS)]
+        with pytest.raises(capi.NBodyError):
+            ctx.snapshot_async()                       # ring full
+        first = ctx.snapshot_wait(tickets[0])
+        assert np.array_equal(first, b[:, 1:4])
+        for t in tickets:
+            ctx.snapshot_release(t)
+        ctx.step(capi.NBODY_RK2, 0.1, 1)
+        t1 = ctx.snapshot_async()                      # taken while nothing is synchronised
+        ctx.step(capi.NBODY_RK2, 0.1, 1)
+        p1 = ctx.snapshot_wait(t1)
+        ctx.sync()
+        p2 = ctx.download_aos()[:, 1:4]
+        assert not np.array_equal(p1, p2)
+        assert rel_inf(p1 + 0.1 * b[:, 4:7], p2) < 1e-3  # one more step of (almost) free streaming
+        tm = ctx.timing()
+        assert tm.steps_done == 2 and tm.force_launches == 2 and tm.interactions == 2 * 300 * 300
+
+
+def test_energy_vs_oracle(oracle):
+    b = generators.plummer_bodies(4000, seed=12)
+    with capi.Context(4000, 64) as ctx:
+        ctx.set_params(6.67e-11, 1e-3)
+        ctx.upload_aos(b)
+        k0, u0 = ctx.energy()
+        ctx.step(capi.NBODY_RK4, 1e-3, 20, sync=True)
+        k1, u1 = ctx.energy()
+        fin = ctx.download_aos()
+    ko, uo = oracle.energy(b, eps=1e-3, threads=8)
+    assert abs(k0 - ko) / abs(ko) < 1e-13 and abs(u0 - uo) / abs(uo) < 1e-12
+    ko1, uo1 = oracle.energy(fin, eps=1e-3, threads=8)
+    assert abs((k1 + u1) - (ko1 + uo1)) / abs(ko1 + uo1) < 1e-11
+    assert abs(u0 / k0 + 2.0) < 0.15                          # virial equilibrium of the model
+    assert abs((k1 + u1) - (k0 + u0)) / abs(k0 + u0) < 1e-6   # RK4 energy drift, 20 steps
+
+
+def test_python_host_mirror_writes_reference_files(golden, tmp_path):
+    sys_ = lab.ode_system()
+    sys_.name, sys_.tau, sys_.t_start, sys_.t_final = "4Body_test", 0.1, 0.0, 20.0
+    sys_.n_time_steps = 200
+    sys_.traj_init = golden["body4"]
+    solver = lab.Solver_N_body(output_folder=str(tmp_path))
+    solver.solve_parallel_CUDA(sys_)
+    lines = open(tmp_path / "results_0.100000.csv").read().splitlines()
+    assert lines[0] + "\n" == lab.LAB4_HEADER and len(lines) == 202
+    rows = np.array([[float(x) for x in l.split(";")[:-1]] for l in lines[1:]])
+    assert np.abs(rows - golden["ref_rk2_4body_0100"]).max() < TOL64_TRAJ
+    tcsv = open(tmp_path / "output_4Body_test_0.100000_np_1.csv").read().splitlines()
+    assert tcsv[0] == "size;t_start;t_finish;tau;time_steps;num_procs;time_taken;avg_time_for_step"
+    assert tcsv[1].startswith("4;0;20;0.1;200;1;")

@@ -1,0 +1,105 @@
+"""CPU-side checks: the C-ABI library loads and exports every declared symbol, refuses to
+run without a GPU (no CPU fallback), and the host mirror of the lab's interface (file
+formats, loop control, generators) behaves like the reference."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import HAS_GPU, ROOT
+from parallel_comp_labs_b200 import capi, generators, lab
+
+
+def test_library_exports_every_declared_symbol():
+    L = capi.lib()
+    names = capi.declared_symbols()
+    assert len(names) >= 20 and "nbody_step" in names and "nbody_rhs" in names
+    missing = [n for n in names if not hasattr(L, n)]
+    assert not missing, missing
+    assert b"sm_100a" in L.nbody_version()
+
+
+def test_library_has_sm100a_code_and_tma():
+    so = capi.LIB_PATH
+    elf = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
+    assert "sm_100a" in elf
+    sass = subprocess.run(["cuobjdump", "-sass", "-fun",
+                           "_ZN5nbody12force_kernelIdLi128ELi2ELi3ELi6ELi1ELi8ELi2EEEvNS_11ForceParamsENS_5ClampIT_EE",
+                           so], capture_output=True, text=True).stdout
+    assert "UBLKCP" in sass          # cp.async.bulk (TMA engine) stages the j-tiles
+    assert "MUFU.RSQ64H" in sass and "DFMA" in sass and "SYNCS" in sass
+
+
+@pytest.mark.skipif(HAS_GPU, reason="this box has a GPU")
+def test_no_cpu_fallback():
+    with pytest.raises(capi.NBodyError) as e:
+        capi.Context(16, 64)
+    assert "no CPU fallback" in str(e.value) or "CUDA" in str(e.value)
+    with pytest.raises(capi.NBodyError):
+        capi.measure_fma_peak(64, 1.0)
+    # the C++ host driver fails loudly too
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    inp = os.path.join(ROOT, "tests", "golden", "_4body.txt")
+    r = subprocess.run([exe, "--input", inp, "--system", "default_test", "--no-traj"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU fallback" in r.stderr
+
+
+def test_argument_errors_without_gpu():
+    L = capi.lib()
+    h = C.c_void_p()
+    assert L.nbody_create(C.byref(h), 0, 64, 0, 0, 1, None) == 1          # n == 0
+    assert L.nbody_create(C.byref(h), 8, 16, 0, 0, 1, None) == 1          # precision
+    assert L.nbody_create(C.byref(h), 4, 64, 0, 0, 5, None) == 1          # world > n
+    assert b"greater than the problem dimension" in L.nbody_last_error(None)
+    assert h.value is None
+
+
+def test_read_data_formats(tmp_path, golden):
+    p = tmp_path / "b.txt"
+    p.write_bytes(b"3 \r\n8.81032e+09  -61.3392 12.7171 -99.7497 -2.99417 -0.402539 1.70019\r\n"
+                  b"1\t2\t3\t4\t\t5\t6\t7\n  1e3 0 0 0 0 0 0")
+    b = lab.read_data(str(p))
+    assert b.shape == (3, 7) and b[0, 0] == 8.81032e9 and b[1, 6] == 7 and b[2, 0] == 1000
+    with pytest.raises(IOError):
+        lab.read_data(str(tmp_path / "missing.txt"))
+
+
+def test_row_format_matches_reference_bytes(golden):
+    """write_bodies_coords output of the reference build, byte for byte."""
+    want = bytes(golden["ref_row_bytes"])
+    got = lab.format_row(0.30000000000000004, golden["body4"][:, 1:4]).encode()
+    assert got == want
+    assert bytes(golden["ref_header"]).decode() == lab.LAB4_HEADER
+    assert lab.lab5_header(4) == ("time;r_1_1;r_1_2;r_1_3;r_2_1;r_2_2;r_2_3;r_3_1;r_3_2;r_3_3;"
+                                  "r_4_1;r_4_2;r_4_3\n")
+
+
+def test_step_count_matches_oracle(oracle):
+    for tau, T in ((0.1, 1), (0.1, 20), (0.05, 20), (0.025, 20), (0.01, 1)):
+        assert lab.step_count(0.0, T, tau) == oracle.step_count(0.0, T, tau)
+        assert lab.step_count(0.0, T, tau, np.float32) == oracle.step_count_f32(0.0, T, tau)
+
+
+def test_generators_are_deterministic_and_sane():
+    a, b = generators.uniform_bodies(1000), generators.uniform_bodies(1000)
+    assert np.array_equal(a, b)
+    assert a[:, 0].min() >= 1e6 and a[:, 0].max() <= 1e8
+    assert np.abs(a[:, 1:4]).max() <= 100 and np.abs(a[:, 4:7]).max() <= 10
+    p = generators.plummer_bodies(20000, seed=0x5EED0003)
+    assert np.array_equal(p, generators.plummer_bodies(20000, seed=0x5EED0003))
+    G = 6.67e-11
+    assert abs(p[:, 0].sum() * G - 1.0) < 1e-12                 # G*M = 1
+    assert np.abs(p[:, 1:4].mean(axis=0)).max() < 1e-12          # centred
+    r = np.linalg.norm(p[:, 1:4], axis=1)
+    assert 1.2 < np.median(r) < 1.4 and r.max() < 24              # half-mass radius 1.305a
+    v2 = (p[:, 4:7] ** 2).sum(axis=1).mean()
+    assert 0.25 < v2 < 0.35                                      # <v^2> = 3 pi/32 (G M / a)
+
+
+def test_host_driver_cli_input_errors(tmp_path):
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    r = subprocess.run([exe, "--input", str(tmp_path / "nope.txt")], capture_output=True, text=True)
+    assert r.returncode == 1 and "file is't open" in r.stdout   # the reference's throw 1
