@@ -160,6 +160,9 @@ class RefLab4:
         L = C.CDLL(REF_SO)
         L.ref_rhs.argtypes = [_dp, _dp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_double,
                               C.c_double]
+        L.ref_rhs_ranks.restype = C.c_double
+        L.ref_rhs_ranks.argtypes = [_dp, _dp, C.c_size_t, C.c_size_t, C.c_int, C.c_double,
+                                    C.c_double]
         L.ref_rk2_run.restype = C.c_double
         L.ref_rk2_run.argtypes = [_dp, C.c_size_t, C.c_double, C.c_double, C.c_double,
                                   C.c_double, C.c_double, C.c_int, C.c_int, C.c_char_p]
@@ -182,6 +185,17 @@ class RefLab4:
         rc = self.L.ref_rhs(b.ctypes.data_as(_dp), d.ctypes.data_as(_dp), n, begin, end, eps, G)
         assert rc == 0
         return d
+
+    def rhs_ranks(self, bodies, rows_per_rank, n_ranks, eps=1e-6, G=6.67e-11, want_diff=False):
+        """Rows [0, rows_per_rank*n_ranks) evaluated by n_ranks thread-ranks through the
+        reference's N_body_func; returns (wall seconds, diff or None)."""
+        b = _aos(bodies, np.float64)
+        d = np.zeros_like(b) if want_diff else None
+        w = self.L.ref_rhs_ranks(b.ctypes.data_as(_dp), d.ctypes.data_as(_dp) if want_diff else None,
+                                 b.shape[0], rows_per_rank, n_ranks, eps, G)
+        if w < 0:
+            raise RuntimeError(f"ref_rhs_ranks failed ({w})")
+        return w, d
 
     def rk2_csv(self, bodies, tau, t_start, t_final, csv_path, eps=1e-6, G=6.67e-11,
                 n_ranks=1, use_bodyr=False) -> float:

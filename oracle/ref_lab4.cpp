@@ -88,6 +88,43 @@ int ref_rhs(const double* aos, double* diff_aos, std::size_t n, std::size_t begi
 	}
 }
 
+/* One RHS evaluation the way P MPI ranks do it inside an RK stage: rank r calls the
+ * reference's N_body_func(traj, diff, begin_r, end_r) on its own copy of the bodies, with
+ * begin_r = r * rows_per_rank (a BOUNDED sample of the rows when rows_per_rank * n_ranks < n;
+ * the timed CPU baseline of bench.py).  diff_aos (n x 7) receives the computed rows.
+ * Returns wall seconds of the slowest rank (MPI_Wtime pair around the call), <0 on error. */
+double ref_rhs_ranks(const double* aos, double* diff_aos, std::size_t n,
+					 std::size_t rows_per_rank, int n_ranks, double eps, double G) {
+	if (rows_per_rank * (std::size_t)n_ranks > n) return -2.;
+	try {
+		std::vector<ode_system<double>> syss(n_ranks);
+		std::vector<std::vector<Body<double>>> diffs(n_ranks);
+		for (int r = 0; r < n_ranks; ++r) {
+			make_system(syss[r], aos, n, 0.1, 0., 1., eps, G, "4Body_random");
+			diffs[r].resize(n);
+		}
+		std::vector<double> t(n_ranks, 0.);
+		mpi_shim::run(n_ranks, [&](int rank) {
+			const std::size_t b = rows_per_rank * (std::size_t)rank;
+			MPI_Barrier(MPI_COMM_WORLD);
+			const double t0 = MPI_Wtime();
+			syss[rank].N_body_func(syss[rank].traj_init, diffs[rank], b, b + rows_per_rank);
+			t[rank] = MPI_Wtime() - t0;
+		});
+		double wall = 0.;
+		for (int r = 0; r < n_ranks; ++r) {
+			const std::size_t b = rows_per_rank * (std::size_t)r;
+			if (diff_aos)
+				std::memcpy(diff_aos + 7 * b, diffs[r].data() + b,
+							rows_per_rank * sizeof(Body<double>));
+			if (t[r] > wall) wall = t[r];
+		}
+		return wall;
+	} catch (...) {
+		return -1.;
+	}
+}
+
 /* Reference RK2 integrator run on n_ranks thread-ranks through the reference's
  * ode_RK2_MPI, with the reference's block partition (class_Solver_N_body.hpp:119-130)
  * restated for the call.  use_bodyr != 0 gathers positions only (MPI_BODYR, the
