@@ -51,7 +51,8 @@ typedef struct nbody_timing {
 } nbody_timing;
 
 /* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
- * distributes the bytes; replaces MPI_Init's rendezvous, lab_4 N_body.cpp:67). */
+ * distributes the bytes; replaces MPI_Init's rendezvous, lab_4 N_body.cpp:67).  One id
+ * creates ONE communicator: every nbody_create of a world needs a fresh id. */
 int nbody_nccl_unique_id(void* out);
 
 /* Create the context of rank `rank` of `world` on CUDA device `device`.

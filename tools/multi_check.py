@@ -1,0 +1,67 @@
+"""Multi-GPU parity check, run under torchrun (one rank per GPU):
+   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+       --master-port 29511 tools/multi_check.py [n]
+Every rank owns a block of i-rows; the packed positions are NCCL-all-gathered per RK stage.
+Checks against the oracle (RHS rows, RK2 + RK4 states) and against a single-GPU run."""
+import os, sys
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+from parallel_comp_labs_b200 import capi, generators
+from oracle import Oracle
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+def fresh_uid():  # one NCCL unique id per communicator (= per context)
+    box = [capi.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 5000
+o = Oracle()
+ok = True
+for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1e-6, 0.1),
+                                 ("plummer", generators.plummer_bodies(n + 37, 32), 1e-3, 1e-3)):
+    nn = bodies.shape[0]
+    for prec, tol in ((64, 1e-12), (32, 1e-4)):
+        with capi.Context(nn, prec, local, rank, world, fresh_uid()) as ctx:
+            ctx.set_params(6.67e-11, eps)
+            ctx.upload_aos(bodies)
+            b, e = ctx.owned_range()
+            a = ctx.rhs().astype(np.float64)
+            want = o.rhs(bodies, b, e, eps=eps, threads=4)[b:e, 4:7]
+            full = o.rhs(bodies, eps=eps, threads=4)[:, 4:7] if rank == 0 and nn <= 20000 else None
+            err = np.abs(a[b:e] - want).max() / max(np.abs(want).max(), 1e-300) if e > b else 0.0
+            assert np.all(np.isnan(a[:b])) and np.all(np.isnan(a[e:]))
+            res = {"rhs": err}
+            for scheme, fn in ((2, o.rk2), (4, o.rk4)):
+                ctx.upload_aos(bodies)
+                ctx.step(scheme, tau, 3)
+                snap = ctx.snapshot()
+                fin = ctx.download_aos().astype(np.float64)
+                k, u = ctx.energy()
+                w, _ = fn(bodies, tau, 0., 1.0, eps=eps, max_steps=3, rows=False, threads=4)
+                res[f"rk{scheme}_r"] = np.abs(fin[:, 1:4] - w[:, 1:4]).max() / np.abs(w[:, 1:4]).max()
+                dv = w[:, 4:7] - bodies[:, 4:7]
+                res[f"rk{scheme}_dv"] = np.abs(fin[:, 4:7] - bodies[:, 4:7] - dv).max() / np.abs(dv).max()
+                res[f"rk{scheme}_snap"] = float(np.abs(snap - fin[:, 1:4]).max())
+                ko, uo = o.energy(w, eps=eps, threads=4)
+                res[f"rk{scheme}_E"] = abs((k + u) - (ko + uo)) / abs(ko + uo)
+            lim = {"rhs": tol, "_r": tol, "_dv": tol * 10, "_snap": 0.0 if prec == 64 else 1e-6,
+                   "_E": max(tol * 10, 1e-9)}
+            good = all(v <= next(l for suf, l in lim.items() if k_.endswith(suf))
+                       for k_, v in res.items())
+            ok &= good
+            print(f"[rank {rank}/{world}] {name} n={nn} fp{prec} rows[{b},{e}) "
+                  + " ".join(f"{k_}={v:.2e}" for k_, v in res.items()) + (" OK" if good else " FAIL"),
+                  flush=True)
+flag = torch.tensor([0 if ok else 1], device="cuda")
+dist.all_reduce(flag)
+dist.barrier()
+dist.destroy_process_group()
+if flag.item():
+    print("MULTI-GPU CHECK FAILED"); sys.exit(1)
+if rank == 0:
+    print("MULTI-GPU CHECK PASSED")
