@@ -344,7 +344,9 @@ def run_b200(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
 # `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
-TRAFFIC_BYTES_PER_LAUNCH = {}
+TRAFFIC_BYTES_PER_LAUNCH = {
+    (1 << 20, 1, 64): 61460992 + 365604864,   # profiles/r01_force_kernel_1M_ncu_full.csv
+}
 
 
 if __name__ == "__main__":
