@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--scheme", default="rk4", choices=["rk2", "rk4"])
     ap.add_argument("--dist", default="plummer", choices=["plummer", "uniform"])
     ap.add_argument("--variant", type=int, default=-1)
+    ap.add_argument("--unimass", type=int, default=-1, help="-1 auto-detect equal masses, 0 off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -240,6 +241,7 @@ def run_b200(args):
     ctx = capi.Context(n, args.precision, local, rank, world, uid)
     ctx.set_params(6.67e-11, eps)
     ctx.set_option("variant", args.variant)
+    ctx.set_option("unimass", args.unimass)
     host_in = capi.PinnedArray((n, 7), dtype)
     host_out = capi.PinnedArray((n, 7), dtype)
     host_in.array[:] = bodies.astype(dtype)
@@ -298,7 +300,9 @@ def run_b200(args):
 
     line = None
     if rank == 0:
-        variant_name = "auto" if args.variant < 0 else str(args.variant)
+        variant_name = {"variant": int(tm.variant), "uniform_mass_factored_out": bool(tm.uniform_mass),
+                        "fp64_instr_per_pair": (15 if tm.uniform_mass else 16) if args.precision == 64
+                        else None}
         line = {
             "metric": "G body-interactions/s", "value": value, "unit": "G interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -48,6 +48,8 @@ typedef struct nbody_timing {
 	uint64_t total_launches;	 /* all kernel launches of this library since create */
 	uint64_t interactions;		 /* body-body interactions evaluated in that call, this rank */
 	uint64_t steps_done;		 /* integrator steps since the last upload */
+	uint32_t uniform_mass;		 /* 1 if the uniform-mass kernels are in use (see "unimass") */
+	uint32_t variant;			 /* force-kernel variant index in use */
 } nbody_timing;
 
 /* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
@@ -82,7 +84,9 @@ int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 int nbody_set_params(nbody_ctx* ctx, double G, double eps);
 
 /* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
- * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (0/1). */
+ * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (0/1),
+ * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
+ * sum, the default; 0 = never; set before the upload). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 
 /* Rows [begin,end) this rank owns (lab_4's offsets[id], counts[id],

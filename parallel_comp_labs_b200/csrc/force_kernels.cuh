@@ -106,23 +106,25 @@ template <> struct Clamp<float> {
 // w = m * x^{-3/2}, x = max(r2,eps2).  ORD = 2: second-order correction of the seed,
 // truncation error (35/16)|e|^3 < 2^-55 (full double accuracy, ~2-3 ulp with rounding);
 // ORD = 1: first-order only, error 1.875 e^2 (|e| measured < 2^-20: <= ~2e-12 relative).
-template <int ORD>
+// UM (uniform mass): every body has the same mass, which is then factored out of the pair
+// sum (a_i = -G m sum_j (r_i-r_j)/den, applied once in K2): one FP64 instruction less.
+template <int ORD, bool UM>
 __device__ __forceinline__ double inv_cube_m(double x, double m) {
 	double y0 = rsqrt_seed(x);				 // MUFU.RSQ64H
 	double t = __dmul_rn(y0, y0);			 // y0^2
 	double e = __fma_rn(-x, t, 1.0);		 // 1 - x y0^2
 	double u = __dmul_rn(y0, t);			 // y0^3
-	double um = __dmul_rn(u, m);			 // m y0^3
+	double um = UM ? u : __dmul_rn(u, m);	 // m y0^3
 	double ue = __dmul_rn(um, e);
 	if (ORD == 1) return __fma_rn(ue, 1.5, um);	 // m y0^3 (1 + 3/2 e)
 	double p = __fma_rn(e, 1.875, 1.5);		 // 3/2 + 15/8 e
 	return __fma_rn(p, ue, um);				 // m y0^3 (1 + e p)
 }
-template <int ORD>
+template <int ORD, bool UM>
 __device__ __forceinline__ float inv_cube_m(float x, float m) {
 	float y = rsqrt_seed(x);  // MUFU.RSQ
 	float y2 = y * y;
-	float my = m * y;
+	float my = UM ? y : m * y;
 	return my * y2;
 }
 
@@ -139,7 +141,7 @@ struct Acc {
 //  EXACT = true: the reference's clamp applied to every pair (cold path; the tile is redone
 //    with it whenever the tracked minimum says some pair -- always including the self pair,
 //    r2 == 0 -- may lie inside the clamp radius).
-template <typename T, int I, int ORD, bool EXACT>
+template <typename T, int I, int ORD, bool UM, bool EXACT>
 __device__ __forceinline__ void interact(const typename V4<T>::type pj, const T (&xi)[I],
 										  const T (&yi)[I], const T (&zi)[I], Acc<T, I>& a,
 										  const Clamp<T>& cl, int& mn) {
@@ -152,7 +154,7 @@ __device__ __forceinline__ void interact(const typename V4<T>::type pj, const T 
 		T r2 = fma(dz, dz, fma(dy, dy, dx * dx));
 		if (EXACT) r2 = cl.apply(r2);
 		else key[k] = Clamp<T>::key(r2);
-		T w = inv_cube_m<ORD>(r2, pj.w);
+		T w = inv_cube_m<ORD, UM>(r2, pj.w);
 		a.x[k] = fma(w, dx, a.x[k]);
 		a.y[k] = fma(w, dy, a.y[k]);
 		a.z[k] = fma(w, dz, a.z[k]);
@@ -184,7 +186,7 @@ template <typename T> struct Tile {
 };
 
 // ---------------------------------------------------------------- the kernel
-template <typename T, int THREADS, int I, int STAGES, int MINB, int JU, int UNROLL, int ORD>
+template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int UNROLL, int ORD>
 __global__ void __launch_bounds__(THREADS, MINB)
 	force_kernel(const ForceParams p, const Clamp<T> cl) {
 	typedef typename V4<T>::type vec4;
@@ -259,12 +261,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			int mn = 0x7fffffff;
 #pragma unroll UNROLL
 			for (int jj = 0; jj < TJ; ++jj)
-				interact<T, I, ORD, false>(tile[jj], xi, yi, zi, acc, cl, mn);
+				interact<T, I, ORD, UM != 0, false>(tile[jj], xi, yi, zi, acc, cl, mn);
 			if (__any_sync(0xffffffffu, mn <= cl.thresh)) {	 // rare: redo this tile exactly
 				acc = saved;
 #pragma unroll 2
 				for (int jj = 0; jj < TJ; ++jj)
-					interact<T, I, ORD, true>(tile[jj], xi, yi, zi, acc, cl, mn);
+					interact<T, I, ORD, UM != 0, true>(tile[jj], xi, yi, zi, acc, cl, mn);
 			}
 			++ring;
 			__syncthreads();  // every warp is done with stage st -> it may be refilled

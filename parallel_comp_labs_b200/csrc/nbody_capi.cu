@@ -64,8 +64,8 @@ thread_local std::string g_err;
 struct Variant {
 	int threads, ipt;  // i-bodies per thread
 	size_t smem;
-	const void* fn;
-	void (*launch)(dim3, cudaStream_t, size_t, const ForceParams&, double eps2);
+	const void* fn[2];	// [0] general masses, [1] uniform mass factored out
+	void (*launch[2])(dim3, cudaStream_t, size_t, const ForceParams&, double eps2);
 	const char* name;
 };
 
@@ -83,37 +83,33 @@ template <> Clamp<float> make_clamp<float>(double eps2) {
 	return c;
 }
 
-template <typename T, int TH, int I, int ST, int MB, int JU, int UN, int ORD>
+template <typename T, int TH, int I, int ST, int MB, int UM, int UN, int ORD>
 void launch_force(dim3 grid, cudaStream_t s, size_t smem, const ForceParams& p, double eps2) {
-	force_kernel<T, TH, I, ST, MB, JU, UN, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
+	force_kernel<T, TH, I, ST, MB, UM, UN, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
 }
-#define NB_VARIANT(T, TH, I, ST, MB, JU, UN, ORD)                                             \
+#define NB_VARIANT(T, TH, I, ST, MB, UN, ORD)                                                  \
 	Variant { TH, I, force_smem_bytes<T, ST>(),                                                \
-			  (const void*)force_kernel<T, TH, I, ST, MB, JU, UN, ORD>,                         \
-			  launch_force<T, TH, I, ST, MB, JU, UN, ORD>,                                      \
-			  #T "/t" #TH "/i" #I "/s" #ST "/b" #MB "/ju" #JU "/u" #UN "/o" #ORD }
+			  {(const void*)force_kernel<T, TH, I, ST, MB, 0, UN, ORD>,                         \
+			   (const void*)force_kernel<T, TH, I, ST, MB, 1, UN, ORD>},                        \
+			  {launch_force<T, TH, I, ST, MB, 0, UN, ORD>, launch_force<T, TH, I, ST, MB, 1, UN, ORD>}, \
+			  #T "/t" #TH "/i" #I "/s" #ST "/b" #MB "/u" #UN "/o" #ORD }
 
-// {threads, i-bodies per thread, ring stages, min CTAs/SM, (unused), j unroll,
+// {threads, i-bodies per thread, ring stages, min CTAs/SM, j unroll,
 //  correction order of the inverse cube (2 = full double accuracy)}
 const Variant g_var64[] = {
-	NB_VARIANT(double, 128, 2, 3, 6, 1, 8, 2),
-	NB_VARIANT(double, 128, 4, 3, 4, 1, 8, 2),
-	NB_VARIANT(double, 128, 2, 3, 6, 1, 16, 2),
-	NB_VARIANT(double, 128, 2, 3, 8, 1, 8, 2),
-	NB_VARIANT(double, 256, 2, 3, 3, 1, 8, 2),
-	NB_VARIANT(double, 64, 2, 3, 12, 1, 8, 2),
-	NB_VARIANT(double, 128, 1, 3, 8, 1, 16, 2),
-	NB_VARIANT(double, 128, 4, 3, 3, 1, 4, 2),
-	NB_VARIANT(double, 128, 2, 3, 6, 1, 8, 1),
-	NB_VARIANT(double, 128, 4, 3, 4, 1, 4, 1),
+	NB_VARIANT(double, 128, 2, 3, 8, 8, 2),	 // default: best at every N measured (profiles/)
+	NB_VARIANT(double, 128, 4, 3, 4, 8, 2),
+	NB_VARIANT(double, 128, 2, 3, 6, 8, 2),
+	NB_VARIANT(double, 256, 2, 3, 3, 8, 2),
+	NB_VARIANT(double, 128, 4, 3, 3, 4, 2),
+	NB_VARIANT(double, 128, 2, 3, 8, 8, 1),	 // first-order correction only
+	NB_VARIANT(double, 128, 4, 3, 4, 8, 1),
 };
 const Variant g_var32[] = {
-	NB_VARIANT(float, 128, 4, 3, 4, 1, 4, 2),
-	NB_VARIANT(float, 128, 8, 3, 4, 1, 4, 2),
-	NB_VARIANT(float, 256, 4, 3, 2, 1, 4, 2),
-	NB_VARIANT(float, 128, 2, 3, 8, 1, 8, 2),
-	NB_VARIANT(float, 256, 8, 3, 2, 1, 2, 2),
-	NB_VARIANT(float, 128, 16, 3, 2, 1, 2, 2),
+	NB_VARIANT(float, 128, 2, 3, 8, 8, 2),
+	NB_VARIANT(float, 128, 4, 3, 4, 4, 2),
+	NB_VARIANT(float, 128, 8, 3, 4, 4, 2),
+	NB_VARIANT(float, 256, 4, 3, 2, 4, 2),
 };
 constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
 constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
@@ -147,6 +143,9 @@ struct nbody_ctx {
 	ncclComm_t comm = nullptr;
 	bool y_gathered = true;
 	bool uploaded = false;
+	bool unimass = false;	   // all bodies share one mass: factored out of the pair sum
+	double uniform_mass = 0.;
+	long opt_unimass = -1;	   // -1 auto-detect at upload, 0 never
 	long opt_time_kernels = 0, opt_slices = 0, opt_variant = -1, opt_use_graph = 0;
 	int n_sm = 148;
 	nbody_timing tm = {};
@@ -179,14 +178,12 @@ int fail(nbody_ctx* c, int code, const std::string& msg) {
 												 g_nccl.GetErrorString(r__));                 \
 	} while (0)
 
-// variant -1 (default) = auto: measured on B200 (tools/sweep.py), the I=4 kernel wins by ~1.5 %
-// once every CTA slot has many units (large owned N); the I=2 / 6-CTAs-per-SM kernel is the
-// robust choice below that.
+// variant -1 (default) = entry 0 of the table.
 const Variant& variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_VAR64 : N_VAR32;
 	const Variant* tab = c->prec == 64 ? g_var64 : g_var32;
 	long v = c->opt_variant;
-	if (v < 0 || v >= nv) v = (c->prec == 64 && c->own_real >= 200000u) ? 1 : 0;
+	if (v < 0 || v >= nv) v = 0;
 	return tab[v];
 }
 
@@ -228,7 +225,8 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 	const unsigned TJ = 256;
 	lp->n_itiles = (ctx->own_real + itile - 1) / itile;
 	int per_sm = 0;
-	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, v.fn, v.threads, v.smem));
+	CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, v.fn[ctx->unimass ? 1 : 0], v.threads,
+													v.smem));
 	if (per_sm < 1) return fail(ctx, NBODY_ERR_CUDA, "force kernel does not fit on an SM");
 	lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
 	lp->jt_total = ctx->n_pad / TJ;
@@ -275,7 +273,7 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, const void* pos, un
 		e1 = ctx->kev[ctx->kev_used++];
 		CK(cudaEventRecord(e0, ctx->sc));
 	}
-	v.launch(dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
+	v.launch[ctx->unimass ? 1 : 0](dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
 	CK(cudaGetLastError());
 	if (e1) CK(cudaEventRecord(e1, ctx->sc));
 	ctx->tm.force_launches++;
@@ -331,6 +329,7 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_n
 	p.own_pad = ctx->own_pad;
 	p.own_real = ctx->own_real;
 	p.n_slices = lp.s_local + lp.s_remote;
+	p.mass_scale = ctx->unimass ? (T)ctx->uniform_mass : T(1);
 	p.minusG = (T)(-(T)ctx->G);
 	p.c_next = (T)c_next;
 	p.b = (T)b;
@@ -466,12 +465,14 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 	CK(cudaMalloc(&ctx->d_energy, 2 * sizeof(double)));
 	CK(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned)));
 	CK(cudaMemset(ctx->vel_s, 0, (size_t)ctx->own_pad * v4));
-	for (int i = 0; i < N_VAR64; ++i)
-		CK(cudaFuncSetAttribute(g_var64[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-								(int)g_var64[i].smem));
-	for (int i = 0; i < N_VAR32; ++i)
-		CK(cudaFuncSetAttribute(g_var32[i].fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-								(int)g_var32[i].smem));
+	for (int u = 0; u < 2; ++u) {
+		for (int i = 0; i < N_VAR64; ++i)
+			CK(cudaFuncSetAttribute(g_var64[i].fn[u], cudaFuncAttributeMaxDynamicSharedMemorySize,
+									(int)g_var64[i].smem));
+		for (int i = 0; i < N_VAR32; ++i)
+			CK(cudaFuncSetAttribute(g_var32[i].fn[u], cudaFuncAttributeMaxDynamicSharedMemorySize,
+									(int)g_var32[i].smem));
+	}
 	if (ctx->world > 1) {
 		if (!nccl_uid) return fail(ctx, NBODY_ERR_ARG, "world > 1 needs an NCCL unique id");
 		if (!g_nccl.load()) return fail(ctx, NBODY_ERR_NCCL, g_nccl.err);
@@ -555,6 +556,10 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "variant out of range");
 		ctx->opt_variant = value;
 	} else if (k == "use_graph") ctx->opt_use_graph = value;
+	else if (k == "unimass") {
+		if (ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "set \"unimass\" before the upload");
+		ctx->opt_unimass = value;
+	}
 	else return fail(ctx, NBODY_ERR_ARG, "unknown option " + k);
 	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 	return NBODY_OK;
@@ -565,6 +570,26 @@ int nbody_owned_range(const nbody_ctx* ctx, size_t* begin, size_t* end) {
 	*begin = std::min<size_t>(ctx->own0, ctx->n);
 	*end = *begin + ctx->own_real;
 	return NBODY_OK;
+}
+
+// Every body has the same mass (e.g. the Plummer configs, the 4-body test)?  Then the mass is
+// factored out of the pair sum.  `stride` = elements between consecutive masses.
+static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t stride) {
+	bool uni = ctx->opt_unimass != 0;
+	double m0 = 0.;
+	if (ctx->prec == 64) {
+		const double* p = (const double*)masses;
+		m0 = p[0];
+		for (size_t i = 1; uni && i < ctx->n; ++i) uni = p[i * stride] == p[0];
+	} else {
+		const float* p = (const float*)masses;
+		m0 = p[0];
+		for (size_t i = 1; uni && i < ctx->n; ++i) uni = p[i * stride] == p[0];
+	}
+	uni = uni && std::isfinite(m0);
+	if (uni != ctx->unimass && ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+	ctx->unimass = uni;
+	ctx->uniform_mass = uni ? m0 : 0.;
 }
 
 static int upload_common(nbody_ctx* ctx) {
@@ -578,17 +603,19 @@ int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
 	if (!ctx || !bodies) return fail(ctx, NBODY_ERR_ARG, "null argument");
 	CK(cudaSetDevice(ctx->device));
 	const size_t bytes = ctx->n * 7 * ctx->esz;
-	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes));
+	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes + 64));
 	CK(cudaMemcpyAsync(ctx->d_aos, bodies, bytes, cudaMemcpyHostToDevice, ctx->sc));
+	detect_uniform_mass(ctx, bodies, 7);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		pack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>((const double*)ctx->d_aos, ctx->Y, ctx->P,
-														ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
-														ctx->own0, ctx->own_pad);
+		pack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>(
+			(const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+			ctx->own0, ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		pack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>((const float*)ctx->d_aos, ctx->Y, ctx->P,
-													   ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
-													   ctx->own0, ctx->own_pad);
+		pack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>(
+			(const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+			ctx->own0, ctx->own_pad, ctx->unimass ? 1e18f : 0.f,
+			ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaStreamSynchronize(ctx->sc));	 // the host buffer is borrowed for the call only
@@ -612,15 +639,16 @@ int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* 
 	CK(cudaMemcpyAsync(d, m, n * e, cudaMemcpyHostToDevice, ctx->sc));
 	CK(cudaMemcpyAsync(dr, r4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
 	CK(cudaMemcpyAsync(dv, v4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
+	detect_uniform_mass(ctx, m, 1);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		pack_soa_kernel<double><<<g, 256, 0, ctx->sc>>>((const double*)d, dr, dv, ctx->Y, ctx->P,
-														ctx->vel_n, (unsigned)n, ctx->n_pad,
-														ctx->own0, ctx->own_pad);
+		pack_soa_kernel<double><<<g, 256, 0, ctx->sc>>>(
+			(const double*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
+			ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		pack_soa_kernel<float><<<g, 256, 0, ctx->sc>>>((const float*)d, dr, dv, ctx->Y, ctx->P,
-													   ctx->vel_n, (unsigned)n, ctx->n_pad,
-													   ctx->own0, ctx->own_pad);
+		pack_soa_kernel<float><<<g, 256, 0, ctx->sc>>>(
+			(const float*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
+			ctx->own_pad, ctx->unimass ? 1e18f : 0.f, ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaStreamSynchronize(ctx->sc));
@@ -730,6 +758,11 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 		}
 		ctx->tm.force_ms = f;
 		ctx->timing_pending = false;
+	}
+	ctx->tm.uniform_mass = ctx->unimass ? 1u : 0u;
+	{
+		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;
+		ctx->tm.variant = (ctx->opt_variant < 0 || ctx->opt_variant >= nv) ? 0u : (uint32_t)ctx->opt_variant;
 	}
 	*out = ctx->tm;
 	return NBODY_OK;

@@ -32,6 +32,7 @@ struct StageParams {
 	void* acc_v;		// V4[own_pad]                    (velocities part)
 	void* rhs_out;		// optional T[3*own_real]: -G*sum only (nbody_rhs test hook)
 	unsigned own0, own_pad, own_real, n_slices;
+	T mass_scale;	 // the uniform mass factored out of K1 (1 when masses differ: exact no-op)
 	T minusG;		 // -G
 	T c_next;		 // a_{s+1,s} * tau (tau/2, tau/2, tau for RK4; tau/2 for RK2)
 	T b;			 // weight of this stage in the final combination
@@ -53,9 +54,9 @@ __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
 		ay = add_rn(ay, q.y);
 		az = add_rn(az, q.z);
 	}
-	ax = mul_rn(ax, p.minusG);
-	ay = mul_rn(ay, p.minusG);
-	az = mul_rn(az, p.minusG);
+	ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
+	ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
+	az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);
 	if (p.rhs_out) {
 		T* o = reinterpret_cast<T*>(p.rhs_out);
 		o[3 * (size_t)i + 0] = ax;
@@ -118,7 +119,8 @@ __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
 // AoS Body<T> (7 x T) -> packed {x,y,z,m} for all n bodies and {vx,vy,vz,0} for owned rows.
 template <typename T>
 __global__ void pack_aos_kernel(const T* __restrict__ aos, void* Yv, void* Pv, void* velv,
-								unsigned n, unsigned n_pad, unsigned own0, unsigned own_pad) {
+								unsigned n, unsigned n_pad, unsigned own0, unsigned own_pad,
+								T pad_pos, T pad_mass) {
 	typedef typename V4<T>::type vec4;
 	vec4* Y = reinterpret_cast<vec4*>(Yv);
 	vec4* P = reinterpret_cast<vec4*>(Pv);
@@ -130,8 +132,12 @@ __global__ void pack_aos_kernel(const T* __restrict__ aos, void* Yv, void* Pv, v
 		const T* b = aos + 7 * (size_t)i;
 		q.x = b[1]; q.y = b[2]; q.z = b[3]; q.w = b[0];
 		v.x = b[4]; v.y = b[5]; v.z = b[6]; v.w = T(0);
-	} else {  // zero-mass pad body at the origin: contributes exactly 0 to every sum
-		q.x = q.y = q.z = q.w = T(0);
+	} else {
+		// pad body: contributes exactly 0 to every sum.  General masses: m = 0 at the origin.
+		// Uniform-mass kernels ignore m, so there the pad sits so far away that y0^3 underflows
+		// to 0 (pad_pos = 1e150 / 1e18; r^2 stays finite).
+		q.x = q.y = q.z = pad_pos;
+		q.w = pad_mass;
 		v.x = v.y = v.z = v.w = T(0);
 	}
 	Y[i] = q;
@@ -143,7 +149,7 @@ __global__ void pack_aos_kernel(const T* __restrict__ aos, void* Yv, void* Pv, v
 template <typename T>
 __global__ void pack_soa_kernel(const T* __restrict__ m, const void* r4v, const void* v4v,
 								void* Yv, void* Pv, void* velv, unsigned n, unsigned n_pad,
-								unsigned own0, unsigned own_pad) {
+								unsigned own0, unsigned own_pad, T pad_pos, T pad_mass) {
 	typedef typename V4<T>::type vec4;
 	const vec4* r4 = reinterpret_cast<const vec4*>(r4v);
 	const vec4* v4 = reinterpret_cast<const vec4*>(v4v);
@@ -159,7 +165,8 @@ __global__ void pack_soa_kernel(const T* __restrict__ m, const void* r4v, const 
 		v = v4[i];
 		v.w = T(0);
 	} else {
-		q.x = q.y = q.z = q.w = T(0);
+		q.x = q.y = q.z = pad_pos;
+		q.w = pad_mass;
 		v.x = v.y = v.z = v.w = T(0);
 	}
 	Y[i] = q;

@@ -25,9 +25,9 @@ def test_library_has_sm100a_code_and_tma():
     so = capi.LIB_PATH
     elf = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
     assert "sm_100a" in elf
-    sass = subprocess.run(["cuobjdump", "-sass", "-fun",
-                           "_ZN5nbody12force_kernelIdLi128ELi2ELi3ELi6ELi1ELi8ELi2EEEvNS_11ForceParamsENS_5ClampIT_EE",
-                           so], capture_output=True, text=True).stdout
+    names = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
+    fn = [l.split()[-1] for l in names.splitlines() if "Function :" in l and "force_kernelId" in l][0]
+    sass = subprocess.run(["cuobjdump", "-sass", "-fun", fn, so], capture_output=True, text=True).stdout
     assert "UBLKCP" in sass          # cp.async.bulk (TMA engine) stages the j-tiles
     assert "MUFU.RSQ64H" in sass and "DFMA" in sass and "SYNCS" in sass
 

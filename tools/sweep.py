@@ -8,6 +8,7 @@ from parallel_comp_labs_b200 import capi, generators
 from oracle import Oracle
 precs = [int(sys.argv[1])] if len(sys.argv) > 1 and sys.argv[1] != "all" else [64, 32]
 ns = [int(a) for a in sys.argv[2:]] or [131072]
+UNIMASS = int(os.environ.get("SWEEP_UNIMASS", "-1"))
 o = Oracle()
 small = generators.plummer_bodies(3000, 5)
 small[7, 1:4] = small[8, 1:4] + 1e-5   # a pair inside the clamp radius
@@ -20,6 +21,7 @@ for prec in precs:
             with capi.Context(3000, prec) as ctx:
                 ctx.set_params(6.67e-11, 1e-3)
                 ctx.set_option("variant", var)
+                ctx.set_option("unimass", UNIMASS)
                 ctx.upload_aos(small)
                 got = ctx.rhs().astype(np.float64)
         except capi.NBodyError as e:
@@ -32,6 +34,7 @@ for prec in precs:
             with capi.Context(n, prec) as ctx:
                 ctx.set_params(6.67e-11, 1e-3)
                 ctx.set_option("variant", var)
+                ctx.set_option("unimass", UNIMASS)
                 ctx.upload_aos(bodies)
                 ts = []
                 for rep in range(3 if n >= 500000 else 5):
