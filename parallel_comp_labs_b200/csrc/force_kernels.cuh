@@ -166,6 +166,34 @@ __device__ __forceinline__ void interact(const typename V4<T>::type pj, const T 
 	}
 }
 
+// ---------------------------------------------------------------- per-thread state ("lane")
+// Scalar lane: I i-bodies and their accumulators in registers, one FP instruction per pair.
+template <typename T, int I, int ORD, bool UM>
+struct LaneScalar {
+	T xi[I], yi[I], zi[I];
+	Acc<T, I> a;
+	__device__ __forceinline__ void init(const T (&x)[I], const T (&y)[I], const T (&z)[I]) {
+#pragma unroll
+		for (int k = 0; k < I; ++k) {
+			xi[k] = x[k]; yi[k] = y[k]; zi[k] = z[k];
+			a.x[k] = a.y[k] = a.z[k] = T(0);
+		}
+	}
+	template <bool EXACT>
+	__device__ __forceinline__ void pair(const typename V4<T>::type pj, const Clamp<T>& cl, int& mn) {
+		interact<T, I, ORD, UM, EXACT>(pj, xi, yi, zi, a, cl, mn);
+	}
+	__device__ __forceinline__ void result(T (&x)[I], T (&y)[I], T (&z)[I]) const {
+#pragma unroll
+		for (int k = 0; k < I; ++k) { x[k] = a.x[k]; y[k] = a.y[k]; z[k] = a.z[k]; }
+	}
+};
+
+// (A packed FP32 lane built on Blackwell's f32x2 instructions -- SASS FADD2/FMUL2/FFMA2, two
+// i-bodies per 64-bit register pair -- was measured in round 1: 2150-2280 G int/s against
+// 2340-2390 for the scalar lane at N = 1M; the packed instructions do not relieve the issue
+// port and the extra pack MOVs cost more than they save.  Not kept.)
+
 // ---------------------------------------------------------------- launch parameters
 struct ForceParams {
 	const void* pos;	   // V4[n_pad], {x,y,z,m}
@@ -239,34 +267,34 @@ __global__ void __launch_bounds__(THREADS, MINB)
 		}
 
 		// i-bodies of this thread: rows own0 + itile*THREADS*I + k*THREADS + tid
-		T xi[I], yi[I], zi[I];
-		Acc<T, I> acc;
+		LaneScalar<T, I, ORD, UM != 0> lane;
 		const unsigned row0 = itile * (THREADS * I) + tid;
+		{
+			T bx[I], by[I], bz[I];
 #pragma unroll
-		for (int k = 0; k < I; ++k) {
-			// the last i-tile may reach past the owned block: clamp the load, drop the store
-			const unsigned row = min(row0 + k * THREADS, p.own_pad - 1u);
-			const vec4 b = pos[(size_t)p.own0 + row];
-			xi[k] = b.x;
-			yi[k] = b.y;
-			zi[k] = b.z;
-			acc.x[k] = acc.y[k] = acc.z[k] = T(0);
+			for (int k = 0; k < I; ++k) {
+				// the last i-tile may reach past the owned block: clamp the load, drop the store
+				const unsigned row = min(row0 + k * THREADS, p.own_pad - 1u);
+				const vec4 b = pos[(size_t)p.own0 + row];
+				bx[k] = b.x;
+				by[k] = b.y;
+				bz[k] = b.z;
+			}
+			lane.init(bx, by, bz);
 		}
 
 		for (unsigned t = 0; t < ntiles; ++t) {
 			const unsigned st = ring % STAGES;
 			mbar_wait(&full[st], (ring / STAGES) & 1u);
 			const vec4* tile = tiles + (size_t)st * TJ;
-			const Acc<T, I> saved = acc;
+			const auto saved = lane;
 			int mn = 0x7fffffff;
 #pragma unroll UNROLL
-			for (int jj = 0; jj < TJ; ++jj)
-				interact<T, I, ORD, UM != 0, false>(tile[jj], xi, yi, zi, acc, cl, mn);
+			for (int jj = 0; jj < TJ; ++jj) lane.template pair<false>(tile[jj], cl, mn);
 			if (__any_sync(0xffffffffu, mn <= cl.thresh)) {	 // rare: redo this tile exactly
-				acc = saved;
+				lane = saved;
 #pragma unroll 2
-				for (int jj = 0; jj < TJ; ++jj)
-					interact<T, I, ORD, UM != 0, true>(tile[jj], xi, yi, zi, acc, cl, mn);
+				for (int jj = 0; jj < TJ; ++jj) lane.template pair<true>(tile[jj], cl, mn);
 			}
 			++ring;
 			__syncthreads();  // every warp is done with stage st -> it may be refilled
@@ -279,12 +307,14 @@ __global__ void __launch_bounds__(THREADS, MINB)
 		}
 
 		vec4* out = apart + (size_t)(p.slice_base + slice) * p.own_pad;
+		T rx[I], ry[I], rz[I];
+		lane.result(rx, ry, rz);
 #pragma unroll
 		for (int k = 0; k < I; ++k) {
 			vec4 o;
-			o.x = acc.x[k];
-			o.y = acc.y[k];
-			o.z = acc.z[k];
+			o.x = rx[k];
+			o.y = ry[k];
+			o.z = rz[k];
 			o.w = T(0);
 			if (row0 + k * THREADS < p.own_pad) out[row0 + k * THREADS] = o;
 		}

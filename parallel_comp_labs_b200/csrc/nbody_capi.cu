@@ -104,6 +104,7 @@ const Variant g_var64[] = {
 	NB_VARIANT(double, 128, 4, 3, 3, 4, 2),
 	NB_VARIANT(double, 128, 2, 3, 8, 8, 1),	 // first-order correction only
 	NB_VARIANT(double, 128, 4, 3, 4, 8, 1),
+	NB_VARIANT(double, 128, 3, 3, 6, 4, 2),
 };
 const Variant g_var32[] = {
 	NB_VARIANT(float, 128, 2, 3, 8, 8, 2),

@@ -21,7 +21,7 @@ for f in re.split(r'\n\s*Function : ', txt)[1:]:
             continue  # not innermost
         body = [i for i in ins if tgt <= i[0] <= addr]
         c = collections.Counter(o.split('.')[0] for _, o, _ in body)
-        if c.get('DFMA', 0) + c.get('FFMA', 0) < 12: continue
+        if c.get('DFMA', 0) + c.get('FFMA', 0) + c.get('FFMA2', 0) < 6: continue
         best = (len(body), c)
         if best:
             c = best[1]
