@@ -301,8 +301,9 @@ def run_b200(args):
     line = None
     if rank == 0:
         variant_name = {"variant": int(tm.variant), "uniform_mass_factored_out": bool(tm.uniform_mass),
-                        "fp64_instr_per_pair": (15 if tm.uniform_mass else 16) if args.precision == 64
-                        else None}
+                        "fp64_instr_per_pair": ((15 if tm.uniform_mass else 16)
+                                                - (1 if tm.variant in (5, 6) else 0))
+                        if args.precision == 64 else None}
         line = {
             "metric": "G body-interactions/s", "value": value, "unit": "G interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -349,7 +350,7 @@ def run_b200(args):
 # dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
 # `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
 TRAFFIC_BYTES_PER_LAUNCH = {
-    (1 << 20, 1, 64): 61460992 + 365604864,   # profiles/r01_force_kernel_1M_ncu_full.csv
+    (1 << 20, 1, 64): 59950080 + 378659840,   # profiles/r01_force_kernel_1M_ncu_full.csv
 }
 
 
