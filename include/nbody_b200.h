@@ -116,7 +116,9 @@ int nbody_sync(nbody_ctx* ctx);
 /* Asynchronous position snapshot (replaces the per-step cudaMemcpyAsync D2H +
  * write_bodies_coords of lab_5 N_body.cu:352-367 and rank 0's row write of lab_4
  * ode_RK2_MPI.hpp:94-96).  Enqueues a device-side pack of all n positions (3 x T per
- * body) and a copy into a pinned ring slot; returns a ticket.  nbody_snapshot_wait
+ * body) and a copy into a pinned ring slot; returns a ticket.  NOT collective: after every
+ * step each rank already holds all positions (the end-of-step all-gather), so rank 0 alone
+ * may take snapshots, as rank 0 alone writes rows in the reference.  nbody_snapshot_wait
  * blocks until that copy has landed and returns the pinned pointer, valid until
  * nbody_snapshot_release.  The ring has NBODY_SNAPSHOT_SLOTS slots; asking for a
  * snapshot while all are held is NBODY_ERR_STATE. */
@@ -127,7 +129,7 @@ int nbody_snapshot_release(nbody_ctx* ctx, uint64_t ticket);
 
 /* Whole state back as n x Body<T> (superset of the reference, whose final state is
  * only visible through the CSV; needed for parity on velocities).  Collective when
- * world > 1 (velocities are owner-local and are gathered here). */
+ * world > 1 (velocities are owner-local and are gathered here): all ranks must call it. */
 int nbody_download_aos(nbody_ctx* ctx, void* bodies);
 
 /* Kinetic and potential energy of the current state, potential consistent with the

@@ -137,12 +137,13 @@ struct nbody_ctx {
 	uint64_t snap_ticket[NBODY_SNAPSHOT_SLOTS] = {};
 	uint64_t next_ticket = 1;
 	cudaStream_t sc = nullptr, sm = nullptr, sx = nullptr;
+	cudaEvent_t e_gy = nullptr;	 // completion of the eager end-of-step gather of Y
 	cudaEvent_t e_k2 = nullptr, e_g = nullptr, e_snap = nullptr, ev_start = nullptr,
 				ev_stop = nullptr;
 	std::vector<cudaEvent_t> kev;  // pairs around force launches (time_kernels)
 	size_t kev_used = 0;
 	ncclComm_t comm = nullptr;
-	bool y_gathered = true;
+	bool y_pending = false;	   // a gather of Y is in flight on sm; sc has not waited for e_gy yet
 	bool uploaded = false;
 	bool unimass = false;	   // all bodies share one mass: factored out of the pair sum
 	double uniform_mass = 0.;
@@ -283,32 +284,40 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, const void* pos, un
 }
 
 // all-gather the owned block of `buf` (V4[n_pad]) across ranks on the comm stream,
-// after everything enqueued so far on sc; leaves e_g recorded on sm.
-int enqueue_gather(nbody_ctx* ctx, void* buf) {
+// after everything enqueued so far on sc; leaves `done` recorded on sm.
+int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
 	CK(cudaEventRecord(ctx->e_k2, ctx->sc));
 	CK(cudaStreamWaitEvent(ctx->sm, ctx->e_k2, 0));
 	const size_t bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
 	char* base = (char*)buf;
 	CKN(g_nccl.AllGather(base + (size_t)ctx->rank * bytes, base, bytes, NCCL_INT8, ctx->comm,
 						 ctx->sm));
-	CK(cudaEventRecord(ctx->e_g, ctx->sm));
+	CK(cudaEventRecord(done, ctx->sm));
 	return NBODY_OK;
 }
 
-// acceleration of the owned rows from positions `pos`; the caller has already made the
-// owned block of `pos` current.  need_gather: the other ranks' blocks are stale.
-int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, void* pos, bool need_gather) {
+enum GatherMode { GATHER_NONE, GATHER_NOW, GATHER_PENDING_Y };
+
+// acceleration of the owned rows from positions `pos`; the owned block of `pos` is current.
+// GATHER_NOW: the other ranks' blocks are stale -> all-gather them now, overlapped with the
+// local-tile launch.  GATHER_PENDING_Y: that gather was already enqueued at the end of the
+// previous step (pos == Y); the remote launch waits for its event.
+int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, void* pos, GatherMode mode) {
 	int rc;
 	ctx->tm.interactions += (uint64_t)ctx->own_real * (uint64_t)ctx->n;	 // self pairs counted,
 	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
 	if (ctx->world == 1)
 		return launch_force_range(ctx, lp, pos, 0, lp.jt_total, lp.s_local, 0);
-	if (need_gather && (rc = enqueue_gather(ctx, pos))) return rc;
+	if (mode == GATHER_NOW && (rc = enqueue_gather(ctx, pos, ctx->e_g))) return rc;
 	// local tiles first: overlaps the all-gather running on sm
 	if ((rc = launch_force_range(ctx, lp, pos, ctx->rank * lp.jt_per_rank, lp.jt_per_rank,
 								 lp.s_local, 0)))
 		return rc;
-	if (need_gather) CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+	if (mode == GATHER_NOW) CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+	if (mode == GATHER_PENDING_Y) {
+		CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
+		ctx->y_pending = false;
+	}
 	return launch_force_range(ctx, lp, pos, (ctx->rank + 1) * lp.jt_per_rank,
 							  lp.jt_total - lp.jt_per_rank, lp.s_remote, lp.s_local);
 }
@@ -366,23 +375,26 @@ int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, int scheme, double tau) {
 	}
 	for (int s = 0; s < ns; ++s) {
 		void* pos = s == 0 ? ctx->Y : ctx->P;
-		const bool need_gather = s == 0 ? !ctx->y_gathered : true;
-		if ((rc = enqueue_forces(ctx, lp, pos, need_gather))) return rc;
-		if (s == 0) ctx->y_gathered = true;
+		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
+		if ((rc = enqueue_forces(ctx, lp, pos, mode))) return rc;
 		const int last = s == ns - 1;
 		if ((rc = stage_dispatch(ctx, lp, nullptr, last ? 0. : c[s], b[s], fs, s == 0, last)))
 			return rc;
 	}
-	ctx->y_gathered = ctx->world == 1;
+	// Eager gather of y_{n+1}: every rank enqueues it here, so Y is whole on all ranks after
+	// every step without any later collective (snapshots, downloads and the energy of ONE rank
+	// only wait for e_gy); the next step's local-tile launch still overlaps it.
+	if (ctx->world > 1) {
+		if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;
+		ctx->y_pending = true;
+	}
 	return NBODY_OK;
 }
 
 int ensure_y_gathered(nbody_ctx* ctx) {
-	if (ctx->y_gathered) return NBODY_OK;
-	int rc = enqueue_gather(ctx, ctx->Y);
-	if (rc) return rc;
-	CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
-	ctx->y_gathered = true;
+	if (!ctx->y_pending) return NBODY_OK;
+	CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
+	ctx->y_pending = false;
 	return NBODY_OK;
 }
 }  // namespace
@@ -424,7 +436,7 @@ void nbody_destroy(nbody_ctx* ctx) {
 		if (ctx->snap_ev[s]) cudaEventDestroy(ctx->snap_ev[s]);
 	}
 	for (cudaEvent_t e : ctx->kev) cudaEventDestroy(e);
-	cudaEvent_t evs[] = {ctx->e_k2, ctx->e_g, ctx->e_snap, ctx->ev_start, ctx->ev_stop};
+	cudaEvent_t evs[] = {ctx->e_k2, ctx->e_g, ctx->e_gy, ctx->e_snap, ctx->ev_start, ctx->ev_stop};
 	for (cudaEvent_t e : evs)
 		if (e) cudaEventDestroy(e);
 	cudaStream_t ss[] = {ctx->sc, ctx->sm, ctx->sx};
@@ -453,6 +465,7 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 	CK(cudaStreamCreateWithFlags(&ctx->sx, cudaStreamNonBlocking));
 	CK(cudaEventCreateWithFlags(&ctx->e_k2, cudaEventDisableTiming));
 	CK(cudaEventCreateWithFlags(&ctx->e_g, cudaEventDisableTiming));
+	CK(cudaEventCreateWithFlags(&ctx->e_gy, cudaEventDisableTiming));
 	CK(cudaEventCreateWithFlags(&ctx->e_snap, cudaEventDisableTiming));
 	CK(cudaEventCreate(&ctx->ev_start));
 	CK(cudaEventCreate(&ctx->ev_stop));
@@ -594,7 +607,7 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 }
 
 static int upload_common(nbody_ctx* ctx) {
-	ctx->y_gathered = true;	 // every rank uploaded the whole array
+	ctx->y_pending = false;	 // every rank uploaded the whole array
 	ctx->uploaded = true;
 	ctx->tm.steps_done = 0;
 	return NBODY_OK;
@@ -680,8 +693,8 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
 	if (!ctx->rhs_out) CK(cudaMalloc(&ctx->rhs_out, (size_t)ctx->own_pad * 3 * ctx->esz));
 	if ((rc = begin_timed_call(ctx))) return rc;
-	if ((rc = enqueue_forces(ctx, lp, ctx->Y, !ctx->y_gathered))) return rc;
-	ctx->y_gathered = true;
+	if ((rc = enqueue_forces(ctx, lp, ctx->Y, ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE)))
+		return rc;
 	if ((rc = stage_dispatch(ctx, lp, ctx->rhs_out, 0., 0., 0., 1, 0))) return rc;
 	if ((rc = end_timed_call(ctx))) return rc;
 	if (ctx->own_real)
@@ -779,10 +792,12 @@ int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
 		if (!ctx->snap_state[s]) { slot = s; break; }
 	if (slot < 0) return fail(ctx, NBODY_ERR_STATE, "all snapshot slots are held");
 	const size_t bytes = ctx->n * 3 * ctx->esz;
-	if (!ctx->snap_dev[slot]) {
-		CK(cudaMalloc(&ctx->snap_dev[slot], bytes));
-		CK(cudaHostAlloc(&ctx->snap_host[slot], bytes, cudaHostAllocDefault));
-		CK(cudaEventCreateWithFlags(&ctx->snap_ev[slot], cudaEventDisableTiming));
+	if (!ctx->snap_dev[0]) {  // first snapshot: set the whole ring up at once
+		for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s) {
+			CK(cudaMalloc(&ctx->snap_dev[s], bytes));
+			CK(cudaHostAlloc(&ctx->snap_host[s], bytes, cudaHostAllocDefault));
+			CK(cudaEventCreateWithFlags(&ctx->snap_ev[s], cudaEventDisableTiming));
+		}
 	}
 	int rc;
 	if ((rc = ensure_y_gathered(ctx))) return rc;
@@ -843,7 +858,7 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
 		if (!ctx->vel_all) CK(cudaMalloc(&ctx->vel_all, (size_t)ctx->n_pad * v4));
 		CK(cudaMemcpyAsync((char*)ctx->vel_all + (size_t)ctx->own0 * v4, ctx->vel_n,
 						   (size_t)ctx->own_pad * v4, cudaMemcpyDeviceToDevice, ctx->sc));
-		if ((rc = enqueue_gather(ctx, ctx->vel_all))) return rc;
+		if ((rc = enqueue_gather(ctx, ctx->vel_all, ctx->e_g))) return rc;
 		CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
 		vel = ctx->vel_all;
 	}

@@ -286,7 +286,8 @@ struct RunOptions {
 
 struct RunResult {
 	long steps = 0;
-	double wall_s = 0, gpu_ms = 0, writer_busy_s = 0;
+	double wall_s = 0, loop_s = 0, gpu_ms = 0, writer_busy_s = 0;  // loop_s: until the GPU is idle;
+	// wall_s additionally includes draining the trajectory writer (the last row's formatting)
 	double interactions = 0;
 	double e_kin0 = 0, e_pot0 = 0, e_kin1 = 0, e_pot1 = 0;
 };
@@ -380,6 +381,7 @@ class Solver_N_body {
 				(void)tm;
 			}
 			if (nbody_sync(ctx)) return fail("sync");
+			res.loop_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
 			if (writer) {
 				writer->finish();
 				res.writer_busy_s = writer->busy_seconds();

@@ -101,10 +101,11 @@ int run(const Args& a) {
 		const double e0 = r.e_kin0 + r.e_pot0, e1 = r.e_kin1 + r.e_pot1;
 		std::printf(
 			"{\"n\": %zu, \"precision\": %d, \"scheme\": \"%s\", \"gpus\": %d, \"steps\": %ld, "
-			"\"wall_s\": %.6f, \"G_interactions_per_s\": %.3f, \"writer_busy_s\": %.6f, "
+			"\"wall_s\": %.6f, \"loop_s\": %.6f, \"G_interactions_per_s\": %.3f, \"writer_busy_s\": %.6f, "
 			"\"energy0\": %.17g, \"energy1\": %.17g, \"energy_drift\": %.3e}\n",
 			sys.traj_init.size(), (int)(8 * sizeof(T)), opt.scheme == NBODY_RK4 ? "rk4" : "rk2",
-			opt.n_gpus, r.steps, r.wall_s, r.interactions / r.wall_s / 1e9, r.writer_busy_s, e0, e1,
+			opt.n_gpus, r.steps, r.wall_s, r.loop_s, r.interactions / r.loop_s / 1e9, r.writer_busy_s, e0,
+			e1,
 			e0 != 0 ? std::fabs(e1 - e0) / std::fabs(e0) : 0.0);
 	}
 	return 0;

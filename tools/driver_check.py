@@ -32,14 +32,17 @@ for g in sorted({1, gpus}):
     n = n_per * g
     inp = f"{tmp}/in_{n}.txt"
     t0 = time.time(); write_bodies(inp, generators.plummer_bodies(n, seed=0x5EED0005)); tw = time.time() - t0
-    off = run(inp, g, 6, False)
-    on = run(inp, g, 6, True)
+    off = run(inp, g, 12, False)
+    on = run(inp, g, 12, True)
     size = os.path.getsize(f"{tmp}/traj.csv")
     res[g] = {"n": n, "off_wall_s": off["wall_s"], "on_wall_s": on["wall_s"],
+              "off_loop_s": off["loop_s"], "on_loop_s": on["loop_s"],
+              "step_time_on_over_off": on["loop_s"] / off["loop_s"],
               "on_over_off": on["wall_s"] / off["wall_s"], "G_int_s_off": off["G_interactions_per_s"],
               "G_int_s_on": on["G_interactions_per_s"], "writer_busy_s": on["writer_busy_s"],
               "traj_bytes": size, "energy_drift": off["energy_drift"]}
-    print(f"gpus={g} n={n}: off {off['wall_s']:.3f}s on {on['wall_s']:.3f}s ratio {on['wall_s']/off['wall_s']:.3f} "
+    print(f"gpus={g} n={n}: loop off {off['loop_s']:.3f}s on {on['loop_s']:.3f}s ratio {on['loop_s']/off['loop_s']:.4f}; "
+          f"wall off {off['wall_s']:.3f}s on {on['wall_s']:.3f}s ratio {on['wall_s']/off['wall_s']:.3f} "
           f"rate {off['G_interactions_per_s']:.0f} G/s writer busy {on['writer_busy_s']:.2f}s traj {size/1e6:.0f} MB", flush=True)
 # multi-GPU parity of the driver: same input on 1 and on G GPUs
 if gpus > 1:
