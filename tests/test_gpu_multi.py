@@ -1,4 +1,4 @@
-"""N > 1 on real GPUs: tools/multi_check.py under torchrun (one rank per GPU, NCCL
+"""N > 1 on real GPUs: tests/tools/multi_check.py under torchrun (one rank per GPU, NCCL
 all-gather of the packed stage positions overlapped with the local-tile force launch).
 Skipped on boxes with fewer than two GPUs (the driver's GPU test box has one); the
 world_size-2 logic is covered on CPU by tests/test_multirank_gloo.py."""
@@ -25,6 +25,6 @@ def _n_gpus():
 def test_two_ranks_match_oracle():
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
                         "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",
-                        "29533", os.path.join(ROOT, "tools", "multi_check.py"), "3000"],
+                        "29533", os.path.join(ROOT, "tests", "tools", "multi_check.py"), "3000"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MULTI-GPU CHECK PASSED" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

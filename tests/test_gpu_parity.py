@@ -131,6 +131,23 @@ def test_rhs_edge_cases(oracle):
     assert rel_inf(got, want) < TOL64_RHS
 
 
+def test_rhs_eps_zero_and_extreme_scales(oracle):
+    b = generators.uniform_bodies(300, seed=13)
+    # eps = 0: the self pair is 0 * (m / 0) = NaN in the reference (struct_ode_system.hpp:69-72)
+    assert np.all(np.isnan(oracle.rhs(b, eps=0.0)[:, 4:7]))
+    assert np.all(np.isnan(gpu_rhs(b, eps=0.0)))
+    # wide dynamic range of positions and masses (still finite r^2)
+    c = b.copy()
+    c[:, 1:4] *= 1e40
+    c[:, 0] *= 1e60
+    want = oracle.rhs(c, eps=1e30)[:, 4:7]
+    assert np.all(np.isfinite(want)) and rel_inf(gpu_rhs(c, eps=1e30), want) < TOL64_RHS
+    d = b.copy()
+    d[:, 1:4] *= 1e-40
+    want = oracle.rhs(d, eps=1e-50)[:, 4:7]
+    assert np.all(np.isfinite(want)) and rel_inf(gpu_rhs(d, eps=1e-50), want) < TOL64_RHS
+
+
 def test_rhs_large_n_row_subsample(oracle):
     """N = 262 144 Plummer: full parity is infeasible on CPU; the oracle evaluates 48 rows
     against all N (exactly the begin,end API).  Plus Newton's third law: sum m_i a_i = 0."""

@@ -1,11 +1,11 @@
 """Multi-GPU parity check, run under torchrun (one rank per GPU):
    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-       --master-port 29511 tools/multi_check.py [n]
+       --master-port 29511 tests/tools/multi_check.py [n]
 Every rank owns a block of i-rows; the packed positions are NCCL-all-gathered per RK stage.
 Checks against the oracle (RHS rows, RK2 + RK4 states) and against a single-GPU run."""
 import os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist

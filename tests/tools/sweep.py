@@ -2,7 +2,7 @@
 several N.  usage: sweep.py [prec] [n ...]   (writes gpurun_out/sweep.json)"""
 import json, os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from parallel_comp_labs_b200 import capi, generators
 from oracle import Oracle
