@@ -136,6 +136,11 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies);
  * clamp force.  Not in the reference.  Collective when world > 1. */
 int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential);
 
+/* Energy plus first moments, out[9] = {kinetic, potential, px, py, pz (sum m v),
+ * mx, my, mz (sum m r; centre of mass = that / M), M (sum m)}, accumulated in FP64.
+ * Not in the reference.  Collective when world > 1. */
+int nbody_diagnostics(nbody_ctx* ctx, double out[9]);
+
 int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out);
 
 /* Pinned host memory for callers that want zero-staging transfers. */

@@ -74,6 +74,7 @@ def lib() -> C.CDLL:
     L.nbody_snapshot_release.argtypes = [vp, C.c_uint64]
     L.nbody_download_aos.argtypes = [vp, vp]
     L.nbody_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.nbody_diagnostics.argtypes = [vp, C.POINTER(C.c_double)]
     L.nbody_get_timing.argtypes = [vp, C.POINTER(Timing)]
     L.nbody_host_alloc.restype = vp
     L.nbody_host_alloc.argtypes = [sz]
@@ -240,6 +241,14 @@ class Context:
         k, u = C.c_double(), C.c_double()
         self._ck(self.L.nbody_energy(self.h, C.byref(k), C.byref(u)))
         return k.value, u.value
+
+    def diagnostics(self) -> dict:
+        d = (C.c_double * 9)()
+        self._ck(self.L.nbody_diagnostics(self.h, d))
+        v = list(d)
+        return {"kinetic": v[0], "potential": v[1], "momentum": np.array(v[2:5]),
+                "mass_moment": np.array(v[5:8]), "mass": v[8],
+                "com": np.array(v[5:8]) / v[8] if v[8] else np.zeros(3)}
 
     def timing(self) -> Timing:
         t = Timing()

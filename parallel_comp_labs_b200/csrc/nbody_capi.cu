@@ -476,7 +476,7 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 	CK(cudaMalloc(&ctx->vel_s, (size_t)ctx->own_pad * v4));
 	CK(cudaMalloc(&ctx->acc_r, (size_t)ctx->own_pad * v4));
 	CK(cudaMalloc(&ctx->acc_v, (size_t)ctx->own_pad * v4));
-	CK(cudaMalloc(&ctx->d_energy, 2 * sizeof(double)));
+	CK(cudaMalloc(&ctx->d_energy, 9 * sizeof(double)));
 	CK(cudaMalloc(&ctx->d_counters, 4 * sizeof(unsigned)));
 	CK(cudaMemset(ctx->vel_s, 0, (size_t)ctx->own_pad * v4));
 	for (int u = 0; u < 2; ++u) {
@@ -878,34 +878,47 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
 	return NBODY_OK;
 }
 
-int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential) {
-	if (!ctx || !kinetic || !potential) return fail(ctx, NBODY_ERR_ARG, "null argument");
-	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "energy before upload");
+int nbody_diagnostics(nbody_ctx* ctx, double out[9]) {
+	if (!ctx || !out) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "diagnostics before upload");
 	CK(cudaSetDevice(ctx->device));
 	int rc;
 	if ((rc = ensure_y_gathered(ctx))) return rc;
-	CK(cudaMemsetAsync(ctx->d_energy, 0, 2 * sizeof(double), ctx->sc));
+	CK(cudaMemsetAsync(ctx->d_energy, 0, 9 * sizeof(double), ctx->sc));
 	if (ctx->own_real) {
 		const unsigned g = (ctx->own_real + 255) / 256;
-		if (ctx->prec == 64)
+		const unsigned gm = std::min(g, 4u * (unsigned)ctx->n_sm);
+		if (ctx->prec == 64) {
 			energy_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
 														  ctx->own0, ctx->own_real, ctx->eps,
 														  ctx->G, ctx->d_energy);
-		else
+			moments_kernel<double><<<gm, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, ctx->own0,
+															ctx->own_real, ctx->d_energy + 2);
+		} else {
 			energy_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
 														 ctx->own0, ctx->own_real, ctx->eps,
 														 ctx->G, ctx->d_energy);
+			moments_kernel<float><<<gm, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, ctx->own0,
+														   ctx->own_real, ctx->d_energy + 2);
+		}
 		CK(cudaGetLastError());
-		ctx->tm.total_launches++;
+		ctx->tm.total_launches += 2;
 	}
 	if (ctx->world > 1)
-		CKN(g_nccl.AllReduce(ctx->d_energy, ctx->d_energy, 2, NCCL_DOUBLE, NCCL_SUM, ctx->comm,
+		CKN(g_nccl.AllReduce(ctx->d_energy, ctx->d_energy, 9, NCCL_DOUBLE, NCCL_SUM, ctx->comm,
 							 ctx->sc));
-	double h[2];
-	CK(cudaMemcpyAsync(h, ctx->d_energy, sizeof(h), cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaMemcpyAsync(out, ctx->d_energy, 9 * sizeof(double), cudaMemcpyDeviceToHost, ctx->sc));
 	CK(cudaStreamSynchronize(ctx->sc));
-	*kinetic = h[0];
-	*potential = h[1];
+	return NBODY_OK;
+}
+
+int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential) {
+	if (!kinetic || !potential) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	double d[9];
+	const int rc = nbody_diagnostics(ctx, d);
+	if (rc) return rc;
+	*kinetic = d[0];
+	*potential = d[1];
 	return NBODY_OK;
 }
 

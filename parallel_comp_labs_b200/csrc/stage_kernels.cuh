@@ -270,6 +270,29 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
+// First moments of the owned rows (diagnostics, FP64 accumulation):
+// out[0..2] += sum m v (momentum), out[3..5] += sum m r, out[6] += sum m.
+template <typename T>
+__global__ void __launch_bounds__(256)
+	moments_kernel(const void* Yv, const void* velv, unsigned own0, unsigned own_real, double* out) {
+	typedef typename V4<T>::type vec4;
+	const vec4* Y = reinterpret_cast<const vec4*>(Yv);
+	const vec4* vel = reinterpret_cast<const vec4*>(velv);
+	double a[7] = {0, 0, 0, 0, 0, 0, 0};
+	for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < own_real; i += gridDim.x * blockDim.x) {
+		const vec4 q = Y[own0 + i], v = vel[i];
+		const double m = q.w;
+		a[0] += m * v.x; a[1] += m * v.y; a[2] += m * v.z;
+		a[3] += m * q.x; a[4] += m * q.y; a[5] += m * q.z;
+		a[6] += m;
+	}
+#pragma unroll
+	for (int k = 0; k < 7; ++k) {
+		for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_down_sync(0xffffffffu, a[k], o);
+		if ((threadIdx.x & 31) == 0) atomicAdd(out + k, a[k]);
+	}
+}
+
 // FMA-pipe peak microbenchmark: 8 independent dependent-chains per thread, register
 // resident, no memory traffic.  flops = 2 * 8 * iters * threads.
 template <typename T>

@@ -13,7 +13,10 @@
 #pragma once
 #include <array>
 #include <atomic>
+#include <algorithm>
 #include <charconv>
+#include <cmath>
+#include <cstdint>
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
@@ -153,6 +156,67 @@ void write_input_format(const std::string& path, const std::vector<Body<T>>& bod
 		}
 		out << line;
 	}
+}
+
+// ---- synthetic inputs ---------------------------------------------------
+// Same counter-based splitmix64 streams as parallel_comp_labs_b200/generators.py.  `uniform` is
+// bit-identical to the Python generator; `plummer` uses the same draws but libm's pow/cos/sin,
+// so it may differ from numpy's in the last ulp.
+inline double splitmix_u01(std::uint64_t seed, std::uint64_t counter) {
+	std::uint64_t z = seed + (counter + 1) * 0x9E3779B97F4A7C15ull;
+	z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+	z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+	z = z ^ (z >> 31);
+	return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// the distributions of the reference's commented-out generate_data (lab_4 N_body.cpp:15-35)
+inline std::vector<Body<double>> generate_uniform(std::size_t n, std::uint64_t seed = 0x5EED0001) {
+	std::vector<Body<double>> b(n);
+	for (std::size_t i = 0; i < n; ++i) {
+		b[i].m = 1e6 + (1e8 - 1e6) * splitmix_u01(seed, 7 * i);
+		for (int k = 0; k < 3; ++k) {
+			b[i].r[k] = -1e2 + 2e2 * splitmix_u01(seed, 7 * i + 1 + k);
+			b[i].v[k] = -1e1 + 2e1 * splitmix_u01(seed, 7 * i + 4 + k);
+		}
+	}
+	return b;
+}
+
+// Plummer sphere, a = 1, G M = 1, equal masses, radius cut 22.8 a (Aarseth-Henon-Wielen)
+inline std::vector<Body<double>> generate_plummer(std::size_t n, std::uint64_t seed = 0x5EED0004,
+												  double G = 6.67e-11, double r_cut = 22.8) {
+	const double pi = 3.14159265358979323846;
+	std::vector<Body<double>> b(n);
+	const std::uint64_t s2 = seed ^ 0xA5A5A5A5ull, s3 = seed ^ 0x3C3C3C3Cull;
+	double com[3] = {0, 0, 0}, vcm[3] = {0, 0, 0};
+	for (std::size_t i = 0; i < n; ++i) {
+		b[i].m = (1.0 / G) / (double)n;
+		double r = 0;
+		for (std::uint64_t a = 0;; ++a) {
+			double x1 = splitmix_u01(seed, 64 * i + a);
+			x1 = std::min(std::max(x1, 1e-12), 1.0 - 1e-12);
+			r = 1.0 / std::sqrt(std::pow(x1, -2.0 / 3.0) - 1.0);
+			if (r <= r_cut) break;
+		}
+		const double x2 = splitmix_u01(s2, 4 * i), x3 = splitmix_u01(s2, 4 * i + 1);
+		double z = (1.0 - 2.0 * x2) * r, rxy = std::sqrt(std::max(r * r - z * z, 0.0));
+		b[i].r = {rxy * std::cos(2 * pi * x3), rxy * std::sin(2 * pi * x3), z};
+		double q = 0;
+		for (std::uint64_t a = 0;; ++a) {
+			const double x4 = splitmix_u01(s3, 512 * i + 2 * a), x5 = splitmix_u01(s3, 512 * i + 2 * a + 1);
+			if (0.1 * x5 < x4 * x4 * std::pow(1.0 - x4 * x4, 3.5)) { q = x4; break; }
+		}
+		const double v = q * std::sqrt(2.0) * std::pow(1.0 + r * r, -0.25);
+		const double x6 = splitmix_u01(s2, 4 * i + 2), x7 = splitmix_u01(s2, 4 * i + 3);
+		z = (1.0 - 2.0 * x6) * v;
+		rxy = std::sqrt(std::max(v * v - z * z, 0.0));
+		b[i].v = {rxy * std::cos(2 * pi * x7), rxy * std::sin(2 * pi * x7), z};
+		for (int k = 0; k < 3; ++k) { com[k] += b[i].r[k]; vcm[k] += b[i].v[k]; }
+	}
+	for (auto& q : b)
+		for (int k = 0; k < 3; ++k) { q.r[k] -= com[k] / (double)n; q.v[k] -= vcm[k] / (double)n; }
+	return b;
 }
 
 // ---- problem descriptor ------------------------------------------------------------------

@@ -43,7 +43,8 @@ void usage() {
 		"           [--t-final 20|1] [--eps 1e-6] [--G 6.67e-11] [--precision 64|32]\n"
 		"           [--scheme rk2|rk4] [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
-		"           [--output-folder ../output] [--variant -1] [--report]");
+		"           [--output-folder ../output] [--variant -1] [--report]\n"
+		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)");
 }
 
 template <typename T>
@@ -128,6 +129,21 @@ int main(int argc, char** argv) {
 		k = k.substr(2);
 		if (i + 1 < argc && std::strncmp(argv[i + 1], "--", 2) != 0) a.kv[k] = argv[++i];
 		else a.kv[k] = "1";
+	}
+	if (a.has("generate")) {  // --generate uniform|plummer --n N [--seed S] --generate-out FILE
+		const std::size_t n = (std::size_t)a.num("n", 0);
+		const std::string kind = a.str("generate", "uniform"), out = a.str("generate-out", "");
+		if (n == 0 || out.empty()) {
+			std::cerr << "--generate needs --n N and --generate-out FILE" << std::endl;
+			return 64;
+		}
+		const bool plummer = kind == "plummer";
+		const std::uint64_t seed =
+			a.has("seed") ? std::strtoull(a.str("seed", "0").c_str(), nullptr, 0)
+						  : (plummer ? 0x5EED0004ull : 0x5EED0001ull);
+		write_input_format(out, plummer ? generate_plummer(n, seed, a.num("G", 6.67e-11))
+										: generate_uniform(n, seed));
+		if (!a.has("input")) return 0;
 	}
 	const int prec = (int)a.num("precision", 64);
 	if (prec == 64) return run<double>(a);

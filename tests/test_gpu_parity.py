@@ -359,6 +359,25 @@ def test_energy_vs_oracle(oracle):
     assert abs((k1 + u1) - (k0 + u0)) / abs(k0 + u0) < 1e-6   # RK4 energy drift, 20 steps
 
 
+def test_momentum_and_com_are_conserved():
+    """Newton's third law at the integrator level: total momentum and the centre-of-mass
+    drift are conserved by RK4 to round-off (size-independent property)."""
+    b = generators.uniform_bodies(6000, seed=17)
+    with capi.Context(6000, 64) as ctx:
+        ctx.upload_aos(b)
+        d0 = ctx.diagnostics()
+        ctx.step(capi.NBODY_RK4, 0.1, 10, sync=True)
+        d1 = ctx.diagnostics()
+    m = b[:, 0]
+    assert abs(d0["mass"] - m.sum()) / m.sum() < 1e-14
+    assert np.abs(d0["momentum"] - (m[:, None] * b[:, 4:7]).sum(0)).max() / np.abs(m[:, None] * b[:, 4:7]).sum() < 1e-14
+    assert np.abs(d0["com"] - (m[:, None] * b[:, 1:4]).sum(0) / m.sum()).max() < 1e-12
+    scale = np.abs(m[:, None] * b[:, 4:7]).sum()
+    assert np.abs(d1["momentum"] - d0["momentum"]).max() / scale < 1e-14
+    v_com = d0["momentum"] / d0["mass"]
+    assert np.abs(d1["com"] - (d0["com"] + v_com * 1.0)).max() < 1e-11
+
+
 def test_python_host_mirror_writes_reference_files(golden, tmp_path):
     sys_ = lab.ode_system()
     sys_.name, sys_.tau, sys_.t_start, sys_.t_final = "4Body_test", 0.1, 0.0, 20.0

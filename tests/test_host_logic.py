@@ -103,3 +103,14 @@ def test_host_driver_cli_input_errors(tmp_path):
     exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
     r = subprocess.run([exe, "--input", str(tmp_path / "nope.txt")], capture_output=True, text=True)
     assert r.returncode == 1 and "file is't open" in r.stdout   # the reference's throw 1
+
+
+def test_cxx_generator_matches_python(tmp_path):
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    u, p = str(tmp_path / "u.txt"), str(tmp_path / "p.txt")
+    assert subprocess.run([exe, "--generate", "uniform", "--n", "777", "--generate-out", u]).returncode == 0
+    assert subprocess.run([exe, "--generate", "plummer", "--n", "1500", "--seed", "0x5EED0003",
+                           "--generate-out", p]).returncode == 0
+    assert np.array_equal(lab.read_data(u), generators.uniform_bodies(777))
+    a, b = lab.read_data(p), generators.plummer_bodies(1500, seed=0x5EED0003)
+    assert np.abs(a - b).max() / np.abs(b).max() < 1e-14
