@@ -84,7 +84,7 @@ int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 int nbody_set_params(nbody_ctx* ctx, double G, double eps);
 
 /* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
- * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (0/1),
+ * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (-1 = auto: CUDA-graph replay of a step when n <= 16384 on one GPU; 0/1),
  * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
  * sum, the default; 0 = never; set before the upload). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);

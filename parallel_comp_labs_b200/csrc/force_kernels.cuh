@@ -206,6 +206,7 @@ struct ForceParams {
 	unsigned jt_total;	   // n_pad / TJ
 	unsigned n_slices;	   // j-slices in this launch
 	unsigned slice_base;   // first slice row of apart written by this launch
+	unsigned n_real;	   // bodies that exist; rows >= n_real of `pos` are padding
 	unsigned* counter;	   // work-unit ticket counter, zeroed before the launch
 };
 
@@ -287,14 +288,26 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			const unsigned st = ring % STAGES;
 			mbar_wait(&full[st], (ring / STAGES) & 1u);
 			const vec4* tile = tiles + (size_t)st * TJ;
+			// bodies of this tile that exist (only the last tile of the array is ragged; for the
+			// reference's 4-body problem that is 4 of 256, which is what keeps a step at
+			// launch latency instead of 250 wasted iterations)
+			unsigned jt_here = p.jt_begin + t0 + t;
+			if (jt_here >= p.jt_total) jt_here -= p.jt_total;
+			const unsigned j_first = jt_here * TJ;
+			const int cnt = j_first >= p.n_real ? 0 : (int)min((unsigned)TJ, p.n_real - j_first);
 			const auto saved = lane;
 			int mn = 0x7fffffff;
+			if (cnt == TJ) {  // full tile: compile-time trip count for the hot loop
 #pragma unroll UNROLL
-			for (int jj = 0; jj < TJ; ++jj) lane.template pair<false>(tile[jj], cl, mn);
+				for (int jj = 0; jj < TJ; ++jj) lane.template pair<false>(tile[jj], cl, mn);
+			} else {
+#pragma unroll 2
+				for (int jj = 0; jj < cnt; ++jj) lane.template pair<false>(tile[jj], cl, mn);
+			}
 			if (__any_sync(0xffffffffu, mn <= cl.thresh)) {	 // rare: redo this tile exactly
 				lane = saved;
 #pragma unroll 2
-				for (int jj = 0; jj < TJ; ++jj) lane.template pair<true>(tile[jj], cl, mn);
+				for (int jj = 0; jj < cnt; ++jj) lane.template pair<true>(tile[jj], cl, mn);
 			}
 			++ring;
 			__syncthreads();  // every warp is done with stage st -> it may be refilled

@@ -148,7 +148,8 @@ struct nbody_ctx {
 	bool unimass = false;	   // all bodies share one mass: factored out of the pair sum
 	double uniform_mass = 0.;
 	long opt_unimass = -1;	   // -1 auto-detect at upload, 0 never
-	long opt_time_kernels = 0, opt_slices = 0, opt_variant = -1, opt_use_graph = 0;
+	long opt_time_kernels = 0, opt_slices = 0, opt_variant = -1;
+	long opt_use_graph = -1;  // -1 auto: replay a captured step when the run is launch-bound
 	int n_sm = 148;
 	nbody_timing tm = {};
 	bool timing_pending = false;
@@ -258,6 +259,7 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, const void* pos, un
 	p.jt_total = lp.jt_total;
 	p.n_slices = n_slices;
 	p.slice_base = slice_base;
+	p.n_real = (unsigned)ctx->n;
 	p.counter = ctx->d_counters + (slice_base ? 1 : 0);
 	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
 	const unsigned long long units = (unsigned long long)lp.n_itiles * n_slices;
@@ -717,8 +719,11 @@ int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps) {
 	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
 	if ((rc = begin_timed_call(ctx))) return rc;
 	long done = 0;
-	// Launch-bound regime (small n, single rank): replay one captured step as a CUDA graph.
-	if (ctx->opt_use_graph && ctx->world == 1 && !ctx->opt_time_kernels && n_steps > 1) {
+	// Launch-bound regime (small n, single rank): replay one captured step as a CUDA graph
+	// (3 nodes per stage: counter memset, K1, K2).  The reference's own 4-body run is pure
+	// launch latency (165 us/step in lab_5_N_body_CUDA/output/res_4body_float_64_.csv:2).
+	const bool graph_on = ctx->opt_use_graph > 0 || (ctx->opt_use_graph < 0 && ctx->n <= 16384);
+	if (graph_on && ctx->world == 1 && !ctx->opt_time_kernels && n_steps >= 1) {
 		if (!ctx->graph || ctx->graph_scheme != scheme || ctx->graph_tau != tau) {
 			if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 			cudaGraph_t g = nullptr;
