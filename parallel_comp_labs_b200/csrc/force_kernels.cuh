@@ -10,18 +10,21 @@
 // Design (not a port of calc_acceleration):
 //  * bodies are packed {x,y,z,m} (double4 / float4): one array is the j-tile source,
 //    the i-body source and the all-gather payload;
-//  * persistent CTAs walk work units (i-tile, j-slice) round-robin; a j-slice is a
+//  * persistent CTAs draw work units (i-tile, j-slice) from a ticket counter; a j-slice is a
 //    run of TJ-body tiles fetched by ONE elected thread with 1-D bulk-async copies
 //    (cp.async.bulk -> SASS UBLKCP) into a STAGES-deep shared-memory ring, completion
 //    signalled through mbarrier transaction counts;
 //  * every thread keeps I i-bodies and their accumulators in registers; each j body is
 //    read from shared memory once per thread (warp-broadcast LDS.128) and reused I times;
-//  * clamp moved onto r^2 (max(d^3,eps^3) == max(d^2,eps^2)^{3/2}) and done on the
-//    integer pipe for FP64 (r^2 >= 0, so the IEEE bit patterns order like integers);
+//  * the clamp moves onto r^2 (max(d^3,eps^3) == max(d^2,eps^2)^{3/2}) and OFF the hot loop:
+//    the hot loop only tracks the smallest key(r^2) it saw (VIMNMX3, one per two pairs); a
+//    warp that may have met a pair inside the clamp radius (always: the self pair) restores
+//    its accumulators and redoes that tile with the exact 64-bit integer max;
 //  * FP64: 1/d^3 from the MUFU.RSQ64H seed y0 with a folded correction
 //      e = 1 - x y0^2,  x^{-3/2} = y0^3 (1 + e(3/2 + 15/8 e)) + O(e^3)
-//    -> 16 FP64-pipe instructions per interaction (3 sub, 3 r^2, 7 inverse-cube*m, 3 FMA);
-//  * FP32: MUFU.RSQ directly (tolerance 1e-4), 14 FP32 issue slots per interaction.
+//    -> 16 FP64-pipe instructions per pair (3 sub, 3 r^2, 7 inverse-cube*m, 3 FMA), 15 when
+//    all masses are equal and the mass is factored out (UM);
+//  * FP32: MUFU.RSQ directly (tolerance 1e-4), 13-14 FP32 issue slots per pair.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
