@@ -39,7 +39,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=1 << 20)
+    ap.add_argument("--bodies", "--n", dest="n", type=int, default=1 << 20,
+                    help="number of bodies (use --bodies under torchrun: its parser claims --n*)")
     ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
     ap.add_argument("--scheme", default="rk4", choices=["rk2", "rk4"])
     ap.add_argument("--dist", default="plummer", choices=["plummer", "uniform"])
