@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -38,7 +39,9 @@ struct NcclApi {
 	ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
 	const char* (*GetErrorString)(ncclResult_t) = nullptr;
 	std::string err;
+	std::mutex mu;
 	bool load() {
+		std::lock_guard<std::mutex> lk(mu);	 // rank threads of one process may race here
 		if (lib) return true;
 		const char* env = getenv("NBODY_NCCL_LIB");
 		const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
