@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--dist", default="plummer", choices=["plummer", "uniform"])
     ap.add_argument("--variant", type=int, default=-1)
     ap.add_argument("--unimass", type=int, default=-1, help="-1 auto-detect equal masses, 0 off")
+    ap.add_argument("--p2p", type=int, default=0,
+                    help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -184,8 +186,11 @@ def workload_config(args, tau, eps, variant):
                         f"strong scaling over --gpus)",
             "n_bodies": args.n, "scheme": args.scheme, "tau": tau, "eps": eps,
             "l2": "flushed between timed steps (256 MiB device write); working set 32 B/body",
-            "parallelism": f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
-                           f"per RK stage overlapped with the local-tile force launch",
+            "parallelism": (f"i-rows over {args.gpus} GPU(s), peer-pull exchange: remote j-tiles "
+                            f"fetched from the peers' HBM by the force kernel's bulk-async copies"
+                            if getattr(args, "p2p", 0) and args.gpus > 1 else
+                            f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
+                            f"per RK stage overlapped with the local-tile force launch"),
             "kernel_variant": variant}
 
 
@@ -241,6 +246,10 @@ def run_b200(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     ctx = capi.Context(n, args.precision, local, rank, world, uid)
+    if args.p2p and world > 1:
+        blobs = [None] * world
+        dist.all_gather_object(blobs, ctx.p2p_export())
+        ctx.p2p_connect(blobs)
     ctx.set_params(6.67e-11, eps)
     ctx.set_option("variant", args.variant)
     ctx.set_option("unimass", args.unimass)

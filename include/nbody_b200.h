@@ -70,6 +70,18 @@ int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank,
 				 const void* nccl_uid);
 void nbody_destroy(nbody_ctx* ctx);
 
+/* Peer-pull exchange (optional; one process per GPU, 2..8 ranks on one NVLink domain).
+ * By default the stage positions travel by one NCCL all-gather per RK stage (the counterpart
+ * of lab_4's MPI_Allgatherv, .../schemes/ode_RK2_MPI.hpp:83,91).  After every rank has called
+ * nbody_p2p_export, the blobs have been exchanged (rank order) and every rank has called
+ * nbody_p2p_connect -- all before the first upload -- there is no collective on the step path
+ * any more: the force kernel's bulk-async copies fetch the other ranks' j-tiles straight from
+ * their HBM over NVLink, gated by per-rank epoch flags.  nbody_download_aos and
+ * nbody_energy / nbody_diagnostics remain collectives. */
+#define NBODY_P2P_HANDLE_BYTES 256
+int nbody_p2p_export(nbody_ctx* ctx, void* handle_out /* NBODY_P2P_HANDLE_BYTES */);
+int nbody_p2p_connect(nbody_ctx* ctx, const void* all_handles /* world x NBODY_P2P_HANDLE_BYTES */);
+
 /* The i-row partition nbody_create uses, as pure host arithmetic (no GPU needed):
  * rank r owns global rows [begin,end); all ranks exchange equal blocks of block_rows
  * rows (padded with zero-mass bodies that contribute exactly 0), block_rows * world >= n.

@@ -19,6 +19,7 @@ HEADER_PATH = os.path.join(os.path.dirname(PKG_DIR), "include", "nbody_b200.h")
 
 NBODY_RK2, NBODY_RK4 = 2, 4
 NCCL_UID_BYTES = 128
+P2P_HANDLE_BYTES = 256
 SNAPSHOT_SLOTS = 4
 
 
@@ -61,6 +62,8 @@ def lib() -> C.CDLL:
     L.nbody_destroy.restype = None
     L.nbody_partition.argtypes = [sz, C.c_int, C.c_int, C.POINTER(sz), C.POINTER(sz),
                                   C.POINTER(sz)]
+    L.nbody_p2p_export.argtypes = [vp, vp]
+    L.nbody_p2p_connect.argtypes = [vp, vp]
     L.nbody_set_params.argtypes = [vp, C.c_double, C.c_double]
     L.nbody_set_option.argtypes = [vp, C.c_char_p, C.c_long]
     L.nbody_owned_range.argtypes = [vp, C.POINTER(sz), C.POINTER(sz)]
@@ -171,6 +174,16 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def p2p_export(self) -> bytes:
+        buf = C.create_string_buffer(P2P_HANDLE_BYTES)
+        self._ck(self.L.nbody_p2p_export(self.h, buf))
+        return buf.raw
+
+    def p2p_connect(self, blobs: list[bytes]):
+        """blobs: every rank's p2p_export() result, in rank order."""
+        assert len(blobs) == self.world and all(len(b) == P2P_HANDLE_BYTES for b in blobs)
+        self._ck(self.L.nbody_p2p_connect(self.h, b"".join(blobs)))
 
     def set_params(self, G=6.67e-11, eps=1e-6):
         self._ck(self.L.nbody_set_params(self.h, G, eps))

@@ -199,7 +199,13 @@ struct LaneScalar {
 
 // ---------------------------------------------------------------- launch parameters
 struct ForceParams {
-	const void* pos;	   // V4[n_pad], {x,y,z,m}
+	// Positions {x,y,z,m} as one block of `jt_per_rank` j-tiles per rank.  With NCCL all-gathers
+	// all blocks live in this GPU's own array (blk[r] = pos + r*block); with the peer-pull
+	// exchange (nbody_p2p_connect) blk[r] for r != rank points INTO RANK r's HBM over NVLink and
+	// the bulk-async copies fetch the remote tiles directly: no separate collective.
+	const void* blk[8];
+	unsigned jt_per_rank;  // j-tiles per block
+	unsigned rank;
 	void* apart;		   // V4[n_slices_total][own_pad] raw partial sums (w unused)
 	unsigned own0;		   // first owned global row
 	unsigned own_pad;	   // padded owned rows (row stride of apart)
@@ -217,6 +223,13 @@ template <typename T> struct Tile {
 	static constexpr int TJ = 256;
 };
 
+// global address of j-tile `jt` (absolute tile index): block of its owner + offset inside it
+template <typename vec4, int TJ>
+__device__ __forceinline__ const vec4* tile_src(const ForceParams& p, unsigned jt) {
+	const unsigned r = jt / p.jt_per_rank;
+	return reinterpret_cast<const vec4*>(p.blk[r]) + (size_t)(jt - r * p.jt_per_rank) * TJ;
+}
+
 // ---------------------------------------------------------------- the kernel
 template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int UNROLL, int ORD>
 __global__ void __launch_bounds__(THREADS, MINB)
@@ -231,7 +244,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	volatile unsigned* next_unit_s = reinterpret_cast<volatile unsigned*>(full + STAGES);
 
 	const int tid = threadIdx.x;
-	const vec4* __restrict__ pos = reinterpret_cast<const vec4*>(p.pos);
+	const vec4* __restrict__ own = reinterpret_cast<const vec4*>(p.blk[p.rank]);
 	vec4* __restrict__ apart = reinterpret_cast<vec4*>(p.apart);
 
 	if (tid == 0) {
@@ -266,7 +279,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 				unsigned jt = p.jt_begin + t0 + k;
 				if (jt >= p.jt_total) jt -= p.jt_total;
 				mbar_expect_tx(&full[st], TILE_BYTES);
-				bulk_g2s(tiles + (size_t)st * TJ, pos + (size_t)jt * TJ, TILE_BYTES, &full[st]);
+				bulk_g2s(tiles + (size_t)st * TJ, tile_src<vec4, TJ>(p, jt), TILE_BYTES, &full[st]);
 			}
 		}
 
@@ -279,7 +292,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			for (int k = 0; k < I; ++k) {
 				// the last i-tile may reach past the owned block: clamp the load, drop the store
 				const unsigned row = min(row0 + k * THREADS, p.own_pad - 1u);
-				const vec4 b = pos[(size_t)p.own0 + row];
+				const vec4 b = own[row];
 				bx[k] = b.x;
 				by[k] = b.y;
 				bz[k] = b.z;
@@ -318,7 +331,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 				unsigned jt = p.jt_begin + t0 + t + STAGES;
 				if (jt >= p.jt_total) jt -= p.jt_total;
 				mbar_expect_tx(&full[st], TILE_BYTES);
-				bulk_g2s(tiles + (size_t)st * TJ, pos + (size_t)jt * TJ, TILE_BYTES, &full[st]);
+				bulk_g2s(tiles + (size_t)st * TJ, tile_src<vec4, TJ>(p, jt), TILE_BYTES, &full[st]);
 			}
 		}
 

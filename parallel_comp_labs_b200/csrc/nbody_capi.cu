@@ -146,6 +146,18 @@ struct nbody_ctx {
 	std::vector<cudaEvent_t> kev;  // pairs around force launches (time_kernels)
 	size_t kev_used = 0;
 	ncclComm_t comm = nullptr;
+	// peer-pull exchange (nbody_p2p_connect): remote j-tiles are fetched from the peers' HBM by
+	// the force kernel's bulk-async copies; no all-gather on the step path
+	bool p2p = false;
+	void* P2 = nullptr;				  // second stage buffer (stages alternate P, P2)
+	unsigned* d_flags = nullptr;	  // [8] production epochs published by the peers
+	unsigned** d_peer_flags = nullptr;  // device copy of peer_flags[]
+	void* peerY[8] = {};
+	void* peerP[2][8] = {};			  // [0] = P2 (even stages >= 2), [1] = P (odd stages)
+	unsigned* peer_flags[8] = {};
+	unsigned epoch = 0;				  // productions so far (same sequence on every rank)
+	unsigned epoch_of[3] = {0, 0, 0};  // epoch at which Y, P2, P were last produced
+	bool y_stale = false;			  // p2p: remote blocks of the local Y are out of date
 	bool y_pending = false;	   // a gather of Y is in flight on sm; sc has not waited for e_gy yet
 	bool uploaded = false;
 	bool unimass = false;	   // all bodies share one mass: factored out of the pair sum
@@ -246,13 +258,34 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 	return NBODY_OK;
 }
 
-// one force launch over j-tiles [jt_begin, jt_begin + jt_count) (wrapping)
-int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, const void* pos, unsigned jt_begin,
-					   unsigned jt_count, unsigned n_slices, unsigned slice_base) {
+// Stage position buffers.  X_0 = Y; with NCCL every later stage lives in P; with the
+// peer-pull exchange stages alternate P (odd) / P2 (even) so that a rank never overwrites a
+// block its peers may still be reading.
+enum StageBuf { BUF_Y = 0, BUF_P2 = 1, BUF_P = 2 };
+
+void* buf_ptr(nbody_ctx* ctx, StageBuf b) { return b == BUF_Y ? ctx->Y : b == BUF_P ? ctx->P : ctx->P2; }
+StageBuf stage_buf(const nbody_ctx* ctx, int s) {
+	if (s == 0) return BUF_Y;
+	return (ctx->p2p && (s % 2 == 0)) ? BUF_P2 : BUF_P;
+}
+
+// one force launch over j-tiles [jt_begin, jt_begin + jt_count) (wrapping); `remote` selects
+// the peers' copies of the blocks this rank does not own (peer-pull exchange only)
+int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool remote,
+					   unsigned jt_begin, unsigned jt_count, unsigned n_slices,
+					   unsigned slice_base) {
 	if (lp.n_itiles == 0 || jt_count == 0) return NBODY_OK;
 	const Variant& v = variant_of(ctx);
 	ForceParams p;
-	p.pos = pos;
+	const size_t block_bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
+	for (int r = 0; r < 8; ++r) {
+		const char* base = (const char*)buf_ptr(ctx, buf);
+		if (remote && ctx->p2p && r < ctx->world && r != ctx->rank)
+			base = (const char*)(buf == BUF_Y ? ctx->peerY[r] : ctx->peerP[buf == BUF_P ? 1 : 0][r]);
+		p.blk[r] = r < ctx->world ? base + (size_t)r * block_bytes : nullptr;
+	}
+	p.jt_per_rank = lp.jt_per_rank;
+	p.rank = (unsigned)ctx->rank;
 	p.apart = ctx->apart;
 	p.own0 = ctx->own0;
 	p.own_pad = ctx->own_pad;
@@ -301,40 +334,63 @@ int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
 	return NBODY_OK;
 }
 
+// peer-pull exchange: this rank has just produced its block of `buf` on sc
+int p2p_publish(nbody_ctx* ctx, StageBuf buf) {
+	ctx->epoch++;
+	ctx->epoch_of[buf] = ctx->epoch;
+	p2p_signal_kernel<<<1, 32, 0, ctx->sc>>>(ctx->d_peer_flags, ctx->world, ctx->rank, ctx->epoch);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+int p2p_wait(nbody_ctx* ctx, StageBuf buf) {
+	p2p_wait_kernel<<<1, 32, 0, ctx->sc>>>(ctx->d_flags, ctx->world, ctx->rank, ctx->epoch_of[buf]);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+
 enum GatherMode { GATHER_NONE, GATHER_NOW, GATHER_PENDING_Y };
 
-// acceleration of the owned rows from positions `pos`; the owned block of `pos` is current.
-// GATHER_NOW: the other ranks' blocks are stale -> all-gather them now, overlapped with the
-// local-tile launch.  GATHER_PENDING_Y: that gather was already enqueued at the end of the
-// previous step (pos == Y); the remote launch waits for its event.
-int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, void* pos, GatherMode mode) {
+// acceleration of the owned rows from the positions in `buf`; the owned block is current.
+// NCCL exchange -- GATHER_NOW: the other ranks' blocks are stale -> all-gather them now,
+// overlapped with the local-tile launch; GATHER_PENDING_Y: that gather was already enqueued at
+// the end of the previous step (buf == Y), the remote launch waits for its event.
+// Peer-pull exchange -- the remote launch waits for the peers' epoch flags and then fetches
+// their tiles straight from their HBM.
+int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, GatherMode mode) {
 	int rc;
 	ctx->tm.interactions += (uint64_t)ctx->own_real * (uint64_t)ctx->n;	 // self pairs counted,
 	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
 	if (ctx->world == 1)
-		return launch_force_range(ctx, lp, pos, 0, lp.jt_total, lp.s_local, 0);
-	if (mode == GATHER_NOW && (rc = enqueue_gather(ctx, pos, ctx->e_g))) return rc;
-	// local tiles first: overlaps the all-gather running on sm
-	if ((rc = launch_force_range(ctx, lp, pos, ctx->rank * lp.jt_per_rank, lp.jt_per_rank,
+		return launch_force_range(ctx, lp, buf, false, 0, lp.jt_total, lp.s_local, 0);
+	if (!ctx->p2p && mode == GATHER_NOW && (rc = enqueue_gather(ctx, buf_ptr(ctx, buf), ctx->e_g)))
+		return rc;
+	// local tiles first: overlaps the exchange
+	if ((rc = launch_force_range(ctx, lp, buf, false, ctx->rank * lp.jt_per_rank, lp.jt_per_rank,
 								 lp.s_local, 0)))
 		return rc;
-	if (mode == GATHER_NOW) CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
-	if (mode == GATHER_PENDING_Y) {
-		CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
-		ctx->y_pending = false;
+	if (ctx->p2p) {
+		if ((rc = p2p_wait(ctx, buf))) return rc;
+	} else {
+		if (mode == GATHER_NOW) CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+		if (mode == GATHER_PENDING_Y) {
+			CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
+			ctx->y_pending = false;
+		}
 	}
-	return launch_force_range(ctx, lp, pos, (ctx->rank + 1) * lp.jt_per_rank,
+	return launch_force_range(ctx, lp, buf, true, (ctx->rank + 1) * lp.jt_per_rank,
 							  lp.jt_total - lp.jt_per_rank, lp.s_remote, lp.s_local);
 }
 
 template <typename T>
-int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_next, double b,
-				 double final_scale, int first, int last) {
+int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next_buf,
+				 double c_next, double b, double final_scale, int first, int last) {
 	if (ctx->own_real == 0) return NBODY_OK;
 	StageParams<T> p;
 	p.apart = ctx->apart;
 	p.Y = ctx->Y;
-	p.P = ctx->P;
+	p.P = next_buf;
 	p.vel_n = ctx->vel_n;
 	p.vel_s = ctx->vel_s;
 	p.acc_r = ctx->acc_r;
@@ -357,11 +413,11 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_n
 	return NBODY_OK;
 }
 
-int stage_dispatch(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, double c_next, double b,
-				   double final_scale, int first, int last) {
+int stage_dispatch(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next_buf,
+				   double c_next, double b, double final_scale, int first, int last) {
 	return ctx->prec == 64
-			   ? launch_stage<double>(ctx, lp, rhs_out, c_next, b, final_scale, first, last)
-			   : launch_stage<float>(ctx, lp, rhs_out, c_next, b, final_scale, first, last);
+			   ? launch_stage<double>(ctx, lp, rhs_out, next_buf, c_next, b, final_scale, first, last)
+			   : launch_stage<float>(ctx, lp, rhs_out, next_buf, c_next, b, final_scale, first, last);
 }
 
 // one integrator step, enqueued on sc (+ sm).  tau, c and b are formed in T exactly as
@@ -379,24 +435,43 @@ int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, int scheme, double tau) {
 		else { ns = 4; c[0] = t / 2; c[1] = t / 2; c[2] = t; b[0] = 1.; b[1] = 2.; b[2] = 2.; b[3] = 1.; fs = t / 6; }
 	}
 	for (int s = 0; s < ns; ++s) {
-		void* pos = s == 0 ? ctx->Y : ctx->P;
+		const StageBuf buf = stage_buf(ctx, s);
 		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
-		if ((rc = enqueue_forces(ctx, lp, pos, mode))) return rc;
+		if ((rc = enqueue_forces(ctx, lp, buf, mode))) return rc;
 		const int last = s == ns - 1;
-		if ((rc = stage_dispatch(ctx, lp, nullptr, last ? 0. : c[s], b[s], fs, s == 0, last)))
+		const StageBuf nxt = last ? BUF_Y : stage_buf(ctx, s + 1);
+		if ((rc = stage_dispatch(ctx, lp, nullptr, buf_ptr(ctx, nxt), last ? 0. : c[s], b[s], fs,
+								 s == 0, last)))
 			return rc;
+		if (ctx->p2p && (rc = p2p_publish(ctx, nxt))) return rc;
 	}
-	// Eager gather of y_{n+1}: every rank enqueues it here, so Y is whole on all ranks after
-	// every step without any later collective (snapshots, downloads and the energy of ONE rank
-	// only wait for e_gy); the next step's local-tile launch still overlaps it.
-	if (ctx->world > 1) {
+	if (ctx->p2p) {
+		ctx->y_stale = true;  // the peers' blocks of the local Y are out of date; pulled on demand
+	} else if (ctx->world > 1) {
+		// Eager gather of y_{n+1}: every rank enqueues it here, so Y is whole on all ranks after
+		// every step without any later collective (snapshots, downloads and the energy of ONE
+		// rank only wait for e_gy); the next step's local-tile launch still overlaps it.
 		if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;
 		ctx->y_pending = true;
 	}
 	return NBODY_OK;
 }
 
+// make the local copy of Y whole (snapshots, downloads, diagnostics).  Never a collective.
 int ensure_y_gathered(nbody_ctx* ctx) {
+	if (ctx->p2p) {
+		if (!ctx->y_stale) return NBODY_OK;
+		int rc;
+		if ((rc = p2p_wait(ctx, BUF_Y))) return rc;
+		const size_t block_bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
+		for (int r = 0; r < ctx->world; ++r)
+			if (r != ctx->rank)
+				CK(cudaMemcpyAsync((char*)ctx->Y + (size_t)r * block_bytes,
+								   (const char*)ctx->peerY[r] + (size_t)r * block_bytes, block_bytes,
+								   cudaMemcpyDefault, ctx->sc));
+		ctx->y_stale = false;
+		return NBODY_OK;
+	}
 	if (!ctx->y_pending) return NBODY_OK;
 	CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
 	ctx->y_pending = false;
@@ -430,9 +505,17 @@ void nbody_destroy(nbody_ctx* ctx) {
 	if (ctx->sm) cudaStreamSynchronize(ctx->sm);
 	if (ctx->sx) cudaStreamSynchronize(ctx->sx);
 	if (ctx->graph) cudaGraphExecDestroy(ctx->graph);
+	if (ctx->p2p)
+		for (int r = 0; r < ctx->world; ++r) {
+			if (r == ctx->rank) continue;
+			void* mapped[] = {ctx->peerY[r], ctx->peerP[0][r], ctx->peerP[1][r], ctx->peer_flags[r]};
+			for (void* m : mapped)
+				if (m) cudaIpcCloseMemHandle(m);
+		}
 	if (ctx->comm && g_nccl.lib) g_nccl.CommDestroy(ctx->comm);
 	void* bufs[] = {ctx->Y, ctx->P, ctx->vel_n, ctx->vel_s, ctx->acc_r, ctx->acc_v, ctx->apart,
-					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters};
+					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters,
+					ctx->P2, ctx->d_flags, ctx->d_peer_flags};
 	for (void* b : bufs)
 		if (b) cudaFree(b);
 	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s) {
@@ -493,6 +576,12 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 									(int)g_var32[i].smem));
 	}
 	if (ctx->world > 1) {
+		if (ctx->world <= 8) {	// buffers the peer-pull exchange exports (nbody_p2p_export)
+			CK(cudaMalloc(&ctx->P2, (size_t)ctx->n_pad * v4));
+			CK(cudaMalloc(&ctx->d_flags, 8 * sizeof(unsigned)));
+			CK(cudaMemset(ctx->d_flags, 0, 8 * sizeof(unsigned)));
+			CK(cudaMalloc(&ctx->d_peer_flags, 8 * sizeof(unsigned*)));
+		}
 		if (!nccl_uid) return fail(ctx, NBODY_ERR_ARG, "world > 1 needs an NCCL unique id");
 		if (!g_nccl.load()) return fail(ctx, NBODY_ERR_NCCL, g_nccl.err);
 		ncclUniqueId id;
@@ -556,6 +645,53 @@ int nbody_create(nbody_ctx** out, size_t n, int precision, int device, int rank,
 	return NBODY_OK;
 }
 
+// ---- peer-pull exchange setup ------------------------------------------------------------
+struct P2PHandles {
+	cudaIpcMemHandle_t Y, P2, P, flags;
+};
+static_assert(sizeof(P2PHandles) <= NBODY_P2P_HANDLE_BYTES, "handle blob too small");
+
+int nbody_p2p_export(nbody_ctx* ctx, void* handle_out) {
+	if (!ctx || !handle_out) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (ctx->world < 2 || !ctx->P2)
+		return fail(ctx, NBODY_ERR_STATE, "peer-pull exchange needs 2..8 ranks");
+	CK(cudaSetDevice(ctx->device));
+	P2PHandles h;
+	memset(&h, 0, sizeof(h));
+	CK(cudaIpcGetMemHandle(&h.Y, ctx->Y));
+	CK(cudaIpcGetMemHandle(&h.P2, ctx->P2));
+	CK(cudaIpcGetMemHandle(&h.P, ctx->P));
+	CK(cudaIpcGetMemHandle(&h.flags, ctx->d_flags));
+	memset(handle_out, 0, NBODY_P2P_HANDLE_BYTES);
+	memcpy(handle_out, &h, sizeof(h));
+	return NBODY_OK;
+}
+
+int nbody_p2p_connect(nbody_ctx* ctx, const void* all_handles) {
+	if (!ctx || !all_handles) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (ctx->world < 2 || !ctx->P2)
+		return fail(ctx, NBODY_ERR_STATE, "peer-pull exchange needs 2..8 ranks");
+	if (ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "connect before the first upload");
+	CK(cudaSetDevice(ctx->device));
+	for (int r = 0; r < ctx->world; ++r) {
+		if (r == ctx->rank) {
+			ctx->peer_flags[r] = ctx->d_flags;
+			continue;
+		}
+		P2PHandles h;
+		memcpy(&h, (const char*)all_handles + (size_t)r * NBODY_P2P_HANDLE_BYTES, sizeof(h));
+		CK(cudaIpcOpenMemHandle(&ctx->peerY[r], h.Y, cudaIpcMemLazyEnablePeerAccess));
+		CK(cudaIpcOpenMemHandle(&ctx->peerP[0][r], h.P2, cudaIpcMemLazyEnablePeerAccess));
+		CK(cudaIpcOpenMemHandle(&ctx->peerP[1][r], h.P, cudaIpcMemLazyEnablePeerAccess));
+		void* f = nullptr;
+		CK(cudaIpcOpenMemHandle(&f, h.flags, cudaIpcMemLazyEnablePeerAccess));
+		ctx->peer_flags[r] = (unsigned*)f;
+	}
+	CK(cudaMemcpy(ctx->d_peer_flags, ctx->peer_flags, 8 * sizeof(unsigned*), cudaMemcpyHostToDevice));
+	ctx->p2p = true;
+	return NBODY_OK;
+}
+
 int nbody_set_params(nbody_ctx* ctx, double G, double eps) {
 	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
 	if (!(eps >= 0.)) return fail(ctx, NBODY_ERR_ARG, "eps must be >= 0");
@@ -612,6 +748,14 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 }
 
 static int upload_common(nbody_ctx* ctx) {
+	if (ctx->P2)  // pad rows and masses of the second stage buffer
+		CK(cudaMemcpy(ctx->P2, ctx->P, (size_t)ctx->n_pad * 4 * ctx->esz, cudaMemcpyDeviceToDevice));
+	if (ctx->p2p) {	 // peers read this rank's block of Y from here on: publish it
+		int rc = p2p_publish(ctx, BUF_Y);
+		if (rc) return rc;
+		CK(cudaStreamSynchronize(ctx->sc));
+		ctx->y_stale = false;  // every rank uploaded the whole array
+	}
 	ctx->y_pending = false;	 // every rank uploaded the whole array
 	ctx->uploaded = true;
 	ctx->tm.steps_done = 0;
@@ -698,9 +842,9 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
 	if (!ctx->rhs_out) CK(cudaMalloc(&ctx->rhs_out, (size_t)ctx->own_pad * 3 * ctx->esz));
 	if ((rc = begin_timed_call(ctx))) return rc;
-	if ((rc = enqueue_forces(ctx, lp, ctx->Y, ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE)))
+	if ((rc = enqueue_forces(ctx, lp, BUF_Y, ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE)))
 		return rc;
-	if ((rc = stage_dispatch(ctx, lp, ctx->rhs_out, 0., 0., 0., 1, 0))) return rc;
+	if ((rc = stage_dispatch(ctx, lp, ctx->rhs_out, ctx->P, 0., 0., 0., 1, 0))) return rc;
 	if ((rc = end_timed_call(ctx))) return rc;
 	if (ctx->own_real)
 		CK(cudaMemcpyAsync((char*)acc_host + (size_t)ctx->own0 * 3 * ctx->esz, ctx->rhs_out,

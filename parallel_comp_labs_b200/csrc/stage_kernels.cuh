@@ -293,6 +293,30 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
+// ---------------------------------------------------------------- peer-pull exchange flags
+// After a rank has produced a block of positions (K2 or the upload pack kernel, earlier in the
+// same stream) it publishes the production epoch into every peer's flag array; a peer's remote
+// force launch is preceded by p2p_wait on the epochs it needs.  One launch per GPU, different
+// GPUs: no two waiting kernels ever share a device.
+__global__ void p2p_signal_kernel(unsigned* const* peer_flags, int world, int rank, unsigned epoch) {
+	const int p = threadIdx.x;
+	if (p < world && p != rank) {
+		__threadfence_system();
+		asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flags[p] + rank), "r"(epoch)
+					 : "memory");
+	}
+}
+__global__ void p2p_wait_kernel(const unsigned* flags, int world, int rank, unsigned epoch) {
+	const int p = threadIdx.x;
+	if (p < world && p != rank) {
+		unsigned v;
+		do {
+			asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + p) : "memory");
+			if ((int)(v - epoch) < 0) __nanosleep(200);
+		} while ((int)(v - epoch) < 0);
+	}
+}
+
 // FMA-pipe peak microbenchmark: 8 independent dependent-chains per thread, register
 // resident, no memory traffic.  flops = 2 * 8 * iters * threads.
 template <typename T>

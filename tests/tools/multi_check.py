@@ -20,6 +20,7 @@ def fresh_uid():  # one NCCL unique id per communicator (= per context)
     dist.broadcast_object_list(box, src=0)
     return box[0]
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 5000
+P2P = os.environ.get("NBODY_P2P", "0") == "1"
 o = Oracle()
 ok = True
 for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1e-6, 0.1),
@@ -27,6 +28,10 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
     nn = bodies.shape[0]
     for prec, tol in ((64, 1e-12), (32, 1e-4)):
         with capi.Context(nn, prec, local, rank, world, fresh_uid()) as ctx:
+            if P2P:  # peer-pull exchange instead of NCCL all-gathers
+                blobs = [None] * world
+                dist.all_gather_object(blobs, ctx.p2p_export())
+                ctx.p2p_connect(blobs)
             ctx.set_params(6.67e-11, eps)
             ctx.upload_aos(bodies)
             b, e = ctx.owned_range()
@@ -66,4 +71,4 @@ dist.destroy_process_group()
 if flag.item():
     print("MULTI-GPU CHECK FAILED"); sys.exit(1)
 if rank == 0:
-    print("MULTI-GPU CHECK PASSED")
+    print("MULTI-GPU CHECK PASSED" + (" (peer-pull exchange)" if P2P else " (NCCL all-gather)"))
