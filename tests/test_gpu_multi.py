@@ -32,3 +32,26 @@ def test_two_ranks_match_oracle(p2p, port):
                         port, os.path.join(ROOT, "tests", "tools", "multi_check.py"), "3000"],
                        capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and "MULTI-GPU CHECK PASSED" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs >= 2 GPUs")
+def test_cxx_driver_two_gpus_matches_one(tmp_path):
+    """The C++ host driver with one rank-thread per GPU (NCCL from threads of one process)."""
+    import numpy as np
+    from parallel_comp_labs_b200 import lab
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    inp = str(tmp_path / "in.txt")
+    assert subprocess.run([exe, "--generate", "uniform", "--n", "9000", "--generate-out", inp]).returncode == 0
+    outs = []
+    for g in (1, 2):
+        fin = str(tmp_path / f"f{g}.txt")
+        r = subprocess.run([exe, "--input", inp, "--scheme", "rk4", "--tau", "0.1", "--t-final", "0.25",
+                            "--gpus", str(g), "--final-state", fin, "--timing-out", str(tmp_path / "t.csv"),
+                            "--traj-out", str(tmp_path / f"traj{g}.csv")],
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr + r.stdout
+        outs.append(lab.read_data(fin))
+    assert np.abs(outs[0] - outs[1]).max() / np.abs(outs[0][:, 1:]).max() < 1e-12
+    a = open(tmp_path / "traj1.csv").read().splitlines()
+    b = open(tmp_path / "traj2.csv").read().splitlines()
+    assert len(a) == len(b) == 1 + 1 + 3 and a[0] == b[0]      # header, t_start row, 3 steps
