@@ -125,6 +125,15 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host);
 int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps);
 int nbody_sync(nbody_ctx* ctx);
 
+/* The same fused stage kernel with the tableau as data (not in the
+ * reference): explicit RK schemes whose stage s+1 depends on stage s only,
+ *   k_1 = f(y), k_{s+1} = f(y + tau a_sub[s] k_s),  y += tau scale sum_s b[s] k_s,
+ * e.g. Heun {a={1}, b={1,1}, scale=1/2}, Ralston {a={2/3}, b={1,3}, scale=1/4}, Heun's RK3
+ * {a={1/3,2/3}, b={1,0,3}, scale=1/4}; midpoint and classical RK4 are nbody_step. */
+#define NBODY_MAX_STAGES 8
+int nbody_step_tableau(nbody_ctx* ctx, int n_stages, const double* a_sub /* n_stages-1 */,
+					   const double* b /* n_stages */, double scale, double tau, long n_steps);
+
 /* Asynchronous position snapshot (replaces the per-step cudaMemcpyAsync D2H +
  * write_bodies_coords of lab_5 N_body.cu:352-367 and rank 0's row write of lab_4
  * ode_RK2_MPI.hpp:94-96).  Enqueues a device-side pack of all n positions (3 x T per

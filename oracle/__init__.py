@@ -54,6 +54,10 @@ class Oracle:
             f.restype = C.c_long
             f.argtypes = [_dp, C.c_size_t, C.c_double, C.c_double, C.c_double, C.c_double,
                           C.c_double, _dp, C.c_long, C.c_long, C.c_int]
+        L.oracle_rk_subdiag_f64.restype = C.c_long
+        L.oracle_rk_subdiag_f64.argtypes = [_dp, C.c_size_t, C.c_int, _dp, _dp, C.c_double,
+                                            C.c_double, C.c_double, C.c_double, C.c_double,
+                                            C.c_double, C.c_long, C.c_int]
         L.oracle_rk2_f32.restype = C.c_long
         L.oracle_rk2_f32.argtypes = [_fp, C.c_size_t, C.c_float, C.c_float, C.c_float,
                                      C.c_float, C.c_float, _fp, C.c_long, C.c_long, C.c_int]
@@ -117,6 +121,18 @@ class Oracle:
             rows=True, threads=1):
         return self._run(self.L.oracle_rk4_f64, bodies, tau, t_start, t_final, eps, G,
                          max_steps, rows, threads, np.float64, _dp)
+
+    def rk_subdiag(self, bodies, a, b, scale, tau, t_start, t_final, eps=1e-6, G=6.67e-11,
+                   max_steps=0, threads=1):
+        """Explicit RK with a sub-diagonal tableau (not in the reference); returns the final state."""
+        x = _aos(bodies, np.float64).copy()
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        assert b.size == a.size + 1
+        self.L.oracle_rk_subdiag_f64(x.ctypes.data_as(_dp), x.shape[0], b.size,
+                                     a.ctypes.data_as(_dp), b.ctypes.data_as(_dp), scale, tau,
+                                     t_start, t_final, eps, G, max_steps, threads)
+        return x
 
     def rk2_f32(self, bodies, tau, t_start, t_final, eps=1e-6, G=6.67e-11, max_steps=0,
                 rows=True, threads=1):

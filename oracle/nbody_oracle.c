@@ -290,6 +290,54 @@ long oracle_rk4_f64(body_f64* sol, size_t n, double tau, double t_start,
 	return steps;
 }
 
+/* Explicit RK with a SUB-DIAGONAL tableau (stage s+1 depends on stage s only):
+ *   k_1 = f(y); k_{s+1} = f(y + (tau*a[s]) k_s); y += (tau*scale) * sum_s b[s] k_s
+ * NOT IN THE REFERENCE (generalisation of the reference-style RK2/RK4 loops above; Heun,
+ * Ralston, Heun's RK3 are of this form).  Rounding sequence: c_s = tau*a[s] and
+ * fs = tau*scale formed once; stage vectors multiplied, then added, as in st_mult/st_add. */
+long oracle_rk_subdiag_f64(body_f64* sol, size_t n, int n_stages, const double* a,
+						   const double* b, double scale, double tau, double t_start,
+						   double t_final, double eps, double G, long max_steps, int n_threads) {
+	body_f64* k = (body_f64*)calloc(n, sizeof(body_f64));
+	body_f64* acc = (body_f64*)calloc(n, sizeof(body_f64));
+	body_f64* tmp = (body_f64*)calloc(n, sizeof(body_f64));
+	body_f64* kk = (body_f64*)calloc(n, sizeof(body_f64));
+	for (size_t i = 0; i < n; ++i) tmp[i].m = sol[i].m;
+	long steps = 0;
+	double t = t_start + tau;
+	const double fs = tau * scale;
+	while (1) {
+		oracle_rhs_f64(sol, k, n, 0, n, eps, G, n_threads);
+		memcpy(acc, k, n * sizeof(body_f64));
+		st_mult(acc, b[0], n);
+		for (int s = 0; s + 1 < n_stages; ++s) {
+			memcpy(kk, k, n * sizeof(body_f64));
+			st_mult(kk, tau * a[s], n);
+			for (size_t i = 0; i < n; ++i) {
+				double m = tmp[i].m;
+				tmp[i] = sol[i];
+				tmp[i].m = m;
+			}
+			st_add(tmp, kk, n);
+			oracle_rhs_f64(tmp, k, n, 0, n, eps, G, n_threads);
+			memcpy(kk, k, n * sizeof(body_f64));
+			st_mult(kk, b[s + 1], n);
+			st_add(acc, kk, n);
+		}
+		st_mult(acc, fs, n);
+		st_add(sol, acc, n);
+		++steps;
+		if (max_steps > 0 && steps >= max_steps) break;
+		if (t > t_final) break;
+		t += tau;
+	}
+	free(k);
+	free(acc);
+	free(tmp);
+	free(kk);
+	return steps;
+}
+
 /* FP32 explicit midpoint following the GPU flavour's update form.
  * lab_5_N_body_CUDA/src/N_body.cu:299-316 with mult_n_add (:120-127):
  *   k = f(r,v); r_tmp = r + (tau/2)*k_r; v_tmp = v + (tau/2)*k_v;

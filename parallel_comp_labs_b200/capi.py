@@ -71,6 +71,8 @@ def lib() -> C.CDLL:
     L.nbody_upload_soa.argtypes = [vp, vp, vp, vp]
     L.nbody_rhs.argtypes = [vp, vp]
     L.nbody_step.argtypes = [vp, C.c_int, C.c_double, C.c_long]
+    L.nbody_step_tableau.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                     C.c_double, C.c_double, C.c_long]
     L.nbody_sync.argtypes = [vp]
     L.nbody_snapshot_async.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.nbody_snapshot_wait.argtypes = [vp, C.c_uint64, C.POINTER(vp)]
@@ -216,6 +218,16 @@ class Context:
 
     def step(self, scheme: int, tau: float, n_steps: int = 1, sync: bool = False):
         self._ck(self.L.nbody_step(self.h, scheme, tau, n_steps))
+        if sync:
+            self.sync()
+
+    def step_tableau(self, a_sub, b, scale: float, tau: float, n_steps: int = 1, sync: bool = False):
+        """Explicit RK with a sub-diagonal tableau: k_{s+1} = f(y + tau a_sub[s] k_s),
+        y += tau scale sum b[s] k_s."""
+        a = (C.c_double * max(len(a_sub), 1))(*a_sub)
+        bb = (C.c_double * len(b))(*b)
+        assert len(b) == len(a_sub) + 1
+        self._ck(self.L.nbody_step_tableau(self.h, len(b), a, bb, scale, tau, n_steps))
         if sync:
             self.sync()
 

@@ -420,20 +420,34 @@ int stage_dispatch(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* ne
 			   : launch_stage<float>(ctx, lp, rhs_out, next_buf, c_next, b, final_scale, first, last);
 }
 
-// one integrator step, enqueued on sc (+ sm).  tau, c and b are formed in T exactly as
-// the oracle forms them (tau/2, tau, tau/6 computed in T on the host).
-int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, int scheme, double tau) {
-	int rc;
-	double c[4], b[4], fs;
-	int ns;
+// Coefficients of one step of an explicit RK scheme whose stage s+1 depends on stage s only:
+// stage state = y_n + c[s] k_s, y_{n+1} = y_n + fs * sum_s b[s] k_s (c and fs include tau).
+struct StepCoef {
+	int ns = 0;
+	double c[NBODY_MAX_STAGES] = {}, b[NBODY_MAX_STAGES] = {}, fs = 0;
+};
+
+// tau/2, tau, tau/6 formed in T on the host exactly as the oracle forms them.
+StepCoef builtin_coef(const nbody_ctx* ctx, int scheme, double tau) {
+	StepCoef k;
 	if (ctx->prec == 64) {
-		if (scheme == NBODY_RK2) { ns = 2; c[0] = tau / 2; b[0] = 0.; b[1] = 1.; fs = tau; }
-		else { ns = 4; c[0] = tau / 2; c[1] = tau / 2; c[2] = tau; b[0] = 1.; b[1] = 2.; b[2] = 2.; b[3] = 1.; fs = tau / 6; }
+		if (scheme == NBODY_RK2) { k.ns = 2; k.c[0] = tau / 2; k.b[0] = 0.; k.b[1] = 1.; k.fs = tau; }
+		else { k.ns = 4; k.c[0] = tau / 2; k.c[1] = tau / 2; k.c[2] = tau; k.b[0] = 1.; k.b[1] = 2.; k.b[2] = 2.; k.b[3] = 1.; k.fs = tau / 6; }
 	} else {
 		const float t = (float)tau;
-		if (scheme == NBODY_RK2) { ns = 2; c[0] = t / 2; b[0] = 0.; b[1] = 1.; fs = t; }
-		else { ns = 4; c[0] = t / 2; c[1] = t / 2; c[2] = t; b[0] = 1.; b[1] = 2.; b[2] = 2.; b[3] = 1.; fs = t / 6; }
+		if (scheme == NBODY_RK2) { k.ns = 2; k.c[0] = t / 2; k.b[0] = 0.; k.b[1] = 1.; k.fs = t; }
+		else { k.ns = 4; k.c[0] = t / 2; k.c[1] = t / 2; k.c[2] = t; k.b[0] = 1.; k.b[1] = 2.; k.b[2] = 2.; k.b[3] = 1.; k.fs = t / 6; }
 	}
+	return k;
+}
+
+// one integrator step, enqueued on sc (+ sm)
+int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, const StepCoef& k) {
+	int rc;
+	const int ns = k.ns;
+	const double* c = k.c;
+	const double* b = k.b;
+	const double fs = k.fs;
 	for (int s = 0; s < ns; ++s) {
 		const StageBuf buf = stage_buf(ctx, s);
 		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
@@ -853,10 +867,7 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 	return NBODY_OK;
 }
 
-int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps) {
-	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
-	if (scheme != NBODY_RK2 && scheme != NBODY_RK4)
-		return fail(ctx, NBODY_ERR_ARG, "scheme must be 2 (RK2) or 4 (RK4)");
+static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double tau, long n_steps) {
 	if (n_steps < 0) return fail(ctx, NBODY_ERR_ARG, "n_steps < 0");
 	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step before upload");
 	CK(cudaSetDevice(ctx->device));
@@ -870,34 +881,58 @@ int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps) {
 	// (3 nodes per stage: counter memset, K1, K2).  The reference's own 4-body run is pure
 	// launch latency (165 us/step in lab_5_N_body_CUDA/output/res_4body_float_64_.csv:2).
 	const bool graph_on = ctx->opt_use_graph > 0 || (ctx->opt_use_graph < 0 && ctx->n <= 16384);
-	if (graph_on && ctx->world == 1 && !ctx->opt_time_kernels && n_steps >= 1) {
-		if (!ctx->graph || ctx->graph_scheme != scheme || ctx->graph_tau != tau) {
+	if (graph_on && graph_key > 0 && ctx->world == 1 && !ctx->opt_time_kernels && n_steps >= 1) {
+		if (!ctx->graph || ctx->graph_scheme != graph_key || ctx->graph_tau != tau) {
 			if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 			cudaGraph_t g = nullptr;
 			const nbody_timing keep = ctx->tm;
 			CK(cudaStreamBeginCapture(ctx->sc, cudaStreamCaptureModeThreadLocal));
-			rc = enqueue_step(ctx, lp, scheme, tau);
+			rc = enqueue_step(ctx, lp, k);
 			cudaError_t ce = cudaStreamEndCapture(ctx->sc, &g);
 			ctx->tm = keep;
 			if (rc) return rc;
 			CK(ce);
 			CK(cudaGraphInstantiate(&ctx->graph, g, 0));
 			cudaGraphDestroy(g);
-			ctx->graph_scheme = scheme;
+			ctx->graph_scheme = graph_key;
 			ctx->graph_tau = tau;
 		}
-		const int ns = scheme == NBODY_RK2 ? 2 : 4;
 		for (; done < n_steps; ++done) {
 			CK(cudaGraphLaunch(ctx->graph, ctx->sc));
-			ctx->tm.force_launches += ns;
-			ctx->tm.total_launches += 2 * ns;
-			ctx->tm.interactions += (uint64_t)ns * ctx->own_real * ctx->n;
+			ctx->tm.force_launches += k.ns;
+			ctx->tm.total_launches += 2 * k.ns;
+			ctx->tm.interactions += (uint64_t)k.ns * ctx->own_real * ctx->n;
 		}
 	}
 	for (; done < n_steps; ++done)
-		if ((rc = enqueue_step(ctx, lp, scheme, tau))) return rc;
+		if ((rc = enqueue_step(ctx, lp, k))) return rc;
 	ctx->tm.steps_done += (uint64_t)n_steps;
 	return end_timed_call(ctx);
+}
+
+int nbody_step(nbody_ctx* ctx, int scheme, double tau, long n_steps) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	if (scheme != NBODY_RK2 && scheme != NBODY_RK4)
+		return fail(ctx, NBODY_ERR_ARG, "scheme must be 2 (RK2) or 4 (RK4)");
+	return step_impl(ctx, builtin_coef(ctx, scheme, tau), scheme, tau, n_steps);
+}
+
+int nbody_step_tableau(nbody_ctx* ctx, int n_stages, const double* a_sub, const double* b,
+					   double scale, double tau, long n_steps) {
+	if (!ctx || !b || (n_stages > 1 && !a_sub)) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (n_stages < 1 || n_stages > NBODY_MAX_STAGES)
+		return fail(ctx, NBODY_ERR_ARG, "n_stages out of range");
+	StepCoef k;
+	k.ns = n_stages;
+	if (ctx->prec == 64) {
+		for (int s = 0; s + 1 < n_stages; ++s) k.c[s] = tau * a_sub[s];
+		k.fs = tau * scale;
+	} else {
+		for (int s = 0; s + 1 < n_stages; ++s) k.c[s] = (float)tau * (float)a_sub[s];
+		k.fs = (float)tau * (float)scale;
+	}
+	for (int s = 0; s < n_stages; ++s) k.b[s] = b[s];
+	return step_impl(ctx, k, /*graph_key: tableaux are not cached*/ 0, tau, n_steps);
 }
 
 int nbody_sync(nbody_ctx* ctx) {

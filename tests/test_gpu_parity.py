@@ -233,6 +233,39 @@ def test_known_answer_order_of_accuracy(golden):
     assert abs(errs[(4, 0.1)] - 1.2157e-5) < 5e-8
 
 
+TABLEAUX = {  # name: (a_sub, b, scale)  -- explicit RK, stage s+1 depends on stage s only
+    "heun2": ([1.0], [1.0, 1.0], 0.5),
+    "ralston2": ([2.0 / 3.0], [1.0, 3.0], 0.25),
+    "heun3": ([1.0 / 3.0, 2.0 / 3.0], [1.0, 0.0, 3.0], 0.25),
+    "rk4_as_data": ([0.5, 0.5, 1.0], [1.0, 2.0, 2.0, 1.0], 1.0 / 6.0),
+}
+
+
+@pytest.mark.parametrize("name", list(TABLEAUX))
+def test_step_tableau_vs_oracle(oracle, golden, name):
+    """nbody_step_tableau (tableau as data; not in the reference) against the oracle's generic
+    sub-diagonal integrator, and its order of accuracy on the reference's 4-body problem."""
+    a, b, scale = TABLEAUX[name]
+    bodies = generators.uniform_bodies(1200, seed=33)
+    want = oracle.rk_subdiag(bodies, a, b, scale, 0.1, 0.0, 1.0, max_steps=3, threads=4)
+    with capi.Context(1200, 64) as ctx:
+        ctx.upload_aos(bodies)
+        ctx.step_tableau(a, b, scale, 0.1, 3, sync=True)
+        got = ctx.download_aos()
+    check_state(got, want, bodies, TOL64_TRAJ, steps=3)
+    truth = np.stack([golden[f"traj{k}"][:, 1:4] for k in (1, 2, 3, 4)], axis=1)
+    with capi.Context(4, 64) as ctx:
+        ctx.upload_aos(golden["body4"])
+        pos = []
+        for _ in range(200):
+            ctx.step_tableau(a, b, scale, 0.1, 1)
+            pos.append(ctx.snapshot())
+    err = np.abs(np.array(pos) - truth[1:]).max()
+    lo, hi = {"heun2": (5e-3, 2e-1), "ralston2": (5e-3, 2e-1), "heun3": (1e-4, 1e-2),
+              "rk4_as_data": (5e-6, 5e-5)}[name]
+    assert lo < err < hi, err
+
+
 def test_graph_replay_equals_plain_launches(golden):
     b = generators.uniform_bodies(1500, seed=8)
     a = gpu_run(b, capi.NBODY_RK4, 0.05, 6, graph=0)
