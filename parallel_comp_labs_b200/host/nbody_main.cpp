@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
 #include <iostream>
 #include <map>
 #include <stdexcept>
@@ -44,7 +45,8 @@ void usage() {
 		"           [--scheme rk2|rk4] [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
 		"           [--output-folder ../output] [--variant -1] [--report]\n"
-		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)");
+		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
+		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)");
 }
 
 template <typename T>
@@ -111,6 +113,19 @@ int run(const Args& a) {
 	}
 	return 0;
 }
+// one entry of lab_5's sweep: read_data into SoA vectors, ode_RK2_CUDA(m, r, v, 0, 2, 0.1, path)
+template <typename T>
+void lab5_run(const std::string& in, const std::string& timing_csv) {
+	const std::vector<Body<T>> b = read_data<T>(in);
+	std::vector<T> m(b.size());
+	std::vector<Vec4<T>> r(b.size()), v(b.size());
+	for (std::size_t i = 0; i < b.size(); ++i) {
+		m[i] = b[i].m;
+		r[i] = {b[i].r[0], b[i].r[1], b[i].r[2], T(0)};
+		v[i] = {b[i].v[0], b[i].v[1], b[i].v[2], T(0)};
+	}
+	ode_RK2_CUDA<T>(m, r, v, T(0.), T(2.), T(0.1), timing_csv);
+}
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -144,6 +159,28 @@ int main(int argc, char** argv) {
 		write_input_format(out, plummer ? generate_plummer(n, seed, a.num("G", 6.67e-11))
 										: generate_uniform(n, seed));
 		if (!a.has("input")) return 0;
+	}
+	if (a.has("lab5-sweep")) {	// lab_5's test_random_bodies() (N_body.cu:438-491): RK2, T=[0,2], tau=0.1
+		const std::string dir = a.str("lab5-sweep", "./include");
+		const std::string out = a.str("output-folder", "../output");
+		const int prec5 = (int)a.num("precision", 32);	// the reference's committed typedef is float
+		int ran = 0;
+		for (const char* name : {"10k", "50k", "100k", "500k"}) {
+			const std::string in = dir + "/" + name + "_bodies.txt";
+			if (!std::ifstream(in).good()) continue;  // the reference commits only 10k_bodies.txt
+			try {
+				if (prec5 == 32) lab5_run<float>(in, out + "/res_" + name + "_float_128_.csv");
+				else lab5_run<double>(in, out + "/res_" + name + "_double_128_.csv");
+			} catch (int code) {
+				return code;
+			} catch (const std::exception& e) {
+				std::cerr << "error: " << e.what() << std::endl;
+				return 3;
+			}
+			++ran;
+		}
+		std::cout << "lab5 sweep: " << ran << " input file(s) run" << std::endl;
+		return ran ? 0 : 1;
 	}
 	const int prec = (int)a.num("precision", 64);
 	if (prec == 64) return run<double>(a);

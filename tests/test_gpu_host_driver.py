@@ -76,3 +76,19 @@ def test_random_system_restart_and_report(oracle, tmp_path):
     header, rows = parse(tmp_path / "traj.csv")
     assert rows.shape == (1 + 2, 1 + 3 * 1500)                        # t_start row + every 2nd step
     assert rep["energy_drift"] < 1e-3
+
+
+def test_lab5_sweep_mode(tmp_path):
+    """lab_5's test_random_bodies() (N_body.cu:438-491) as a driver mode: every <name>_bodies.txt
+    present is run with RK2, T=[0,2], tau=0.1 and gets the reference's timing CSV."""
+    inc, out = tmp_path / "include", tmp_path / "output"
+    inc.mkdir()
+    out.mkdir()
+    assert subprocess.run([EXE, "--generate", "uniform", "--n", "10000", "--generate-out",
+                           str(inc / "10k_bodies.txt")]).returncode == 0
+    r = subprocess.run([EXE, "--lab5-sweep", str(inc), "--output-folder", str(out)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "1 input file(s) run" in r.stdout, r.stdout + r.stderr
+    t = open(out / "res_10k_float_128_.csv").read().splitlines()
+    assert t[0] == "type;n_bodies;n_steps;block_size;time_taken;avg_exec_time"
+    assert t[1].startswith("float;10000;20;")   # (2-0)/0.1 in float = 20
