@@ -108,7 +108,8 @@ template <> struct Clamp<float> {
 
 // w = m * x^{-3/2}, x = max(r2,eps2).  ORD = 2: second-order correction of the seed,
 // truncation error (35/16)|e|^3 < 2^-55 (full double accuracy, ~2-3 ulp with rounding);
-// ORD = 1: first-order only, error 1.875 e^2 (|e| measured < 2^-20: <= ~2e-12 relative).
+// ORD = 1: first-order only, error 1.875 e^2 (|e| measured < 2^-19.04: <= 6.5e-12 per pair,
+// 2.5e-13 on a whole RHS); selectable, not the default.
 // UM (uniform mass): every body has the same mass, which is then factored out of the pair
 // sum (a_i = -G m sum_j (r_i-r_j)/den, applied once in K2): one FP64 instruction less.
 template <int ORD, bool UM>
