@@ -11,6 +11,16 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+    # build the product library / driver and the checkers if this checkout has not been built
+    need = [os.path.join(ROOT, "parallel_comp_labs_b200", "libnbody_b200.so"),
+            os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200"),
+            os.path.join(ROOT, "oracle", "_build", "liboracle.so")]
+    if not all(os.path.exists(f) for f in need):
+        import subprocess
+        subprocess.run(["make", "-C", os.path.join(ROOT, "parallel_comp_labs_b200", "csrc")],
+                       check=True, stdout=subprocess.DEVNULL)
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True,
+                       stdout=subprocess.DEVNULL)
 
 
 def _has_gpu() -> bool:
