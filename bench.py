@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 N-body hot path.
+
+Metric (BASELINE.json): G body-interactions/s, FP64 RK4, N = 1 048 576 Plummer sphere
+(configs[3]; it fits one GPU, so N=1 runs the same workload), self pairs counted as the
+reference's loop bounds do: interactions = stages * N^2 * steps.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this framework (CUDA)
+  python bench.py --impl reference [--gpus N] [--steps K] ...    # the reference's CPU path
+
+For N > 1 launch under torchrun (one rank per GPU); strong scaling (N^2 work is fixed).
+One "step" is one RK4 step (4 force evaluations + 4 fused stage kernels, and for N > 1 one
+NCCL all-gather per stage).  `value` is timed with CUDA events on the library's compute
+stream (state resident in HBM), max over ranks; `e2e` goes through the public C-ABI calls
+with pinned HOST buffers (upload + step + download inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+FLOPS_PER_INTERACTION = 20.0          # BASELINE.json / SURVEY.md 8d
+FP64_DATASHEET_TFLOPS = 148 * 64 * 2 * 1.965e9 / 1e12   # 37.2: 64 DFMA lanes/SM/clk @1965 MHz
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--bodies", "--n", dest="n", type=int, default=1 << 20,
+                    help="number of bodies (use --bodies under torchrun: its parser claims --n*)")
+    ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
+    ap.add_argument("--scheme", default="rk4", choices=["rk2", "rk4"])
+    ap.add_argument("--dist", default="plummer", choices=["plummer", "uniform"])
+    ap.add_argument("--variant", type=int, default=-1)
+    ap.add_argument("--unimass", type=int, default=-1, help="-1 auto-detect equal masses, 0 off")
+    ap.add_argument("--p2p", type=int, default=0,
+                    help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-energy", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    return ap.parse_args()
+
+
+def make_bodies(args):
+    from parallel_comp_labs_b200 import generators
+    if args.dist == "plummer":
+        # Plummer, a=1, G*M=1, eps = 1e-3 (clamp radius), tau = 1e-3
+        return generators.plummer_bodies(args.n, seed=0x5EED0004), 1e-3, 1e-3
+    return generators.uniform_bodies(args.n, seed=0x5EED0001), 0.1, 1e-6
+
+
+# ---------------------------------------------------------------- clocks sampler
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._th = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if mask & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        if self.nv:
+            self._th = threading.Thread(target=self._run, daemon=True)
+            self._th.start()
+
+    def stop(self):
+        if self._th:
+            self._stop.set()
+            self._th.join()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------- CPU baseline (reference)
+def cpu_reference_sample(bodies, eps, seconds, steps=1, warmup=0):
+    """Times the reference's own CPU implementation of the path on this box's host cores:
+    oracle/_ref (the reference's lab_4 sources compiled unmodified) when that build
+    travelled here, else the C port.  A BOUNDED sample of the same workload: P thread-ranks
+    each evaluate a block of i-rows of one RK stage's RHS against all N bodies through the
+    reference's N_body_func(traj, diff, begin, end).  Returns (G int/s per step list, info)."""
+    from oracle import Oracle, RefLab4
+    n = bodies.shape[0]
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    cores = max(1, min(cores, n))
+    use_ref = RefLab4.available()
+    if use_ref:
+        ref = RefLab4()
+        run = lambda rows: ref.rhs_ranks(bodies, rows, cores, eps=eps)[0]
+        kind = "reference"
+    else:
+        o = Oracle()
+
+        def run(rows):
+            t0 = time.perf_counter()
+            o.rhs(bodies, 0, rows * cores, eps=eps, threads=cores)
+            return time.perf_counter() - t0
+        kind = "port"
+    rows = 1
+    t = run(rows)
+    per_row = max(t / rows, 1e-9)
+    rows = int(max(1, min(n // cores, seconds / max(steps + warmup, 1) / per_row)))
+    rates = []
+    for k in range(warmup + steps):
+        t = run(rows)
+        if k >= warmup:
+            rates.append(cores * rows * n / t / 1e9)
+    info = {"cores": cores, "kind": kind, "unit": "G interactions/s",
+            "sample": f"one RK-stage RHS: rows [0,{cores * rows}) of N={n} against all N bodies, "
+                      f"{cores} thread-ranks x {rows} rows through the reference's N_body_func "
+                      f"(lab_4 struct_ode_system.hpp:105-128), FP64"}
+    return rates, info
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # the CPU arm runs once, on rank 0
+    bodies, tau, eps = make_bodies(args)
+    rates, info = cpu_reference_sample(bodies, eps, seconds=max(20.0, 4.0 * (args.steps + args.warmup)),
+                                       steps=args.steps, warmup=args.warmup)
+    value = float(np.mean(rates))
+    stages = 4 if args.scheme == "rk4" else 2
+    n = args.n
+    line = {
+        "impl": "reference", "metric": "G body-interactions/s", "value": value,
+        "unit": "G interactions/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": stages * n * n / (value * 1e9) * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": workload_config(args, tau, eps, None),
+        "cpu_baseline": dict(info, value=value),
+        "e2e": {"value": value, "unit": "G interactions/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "note": "reference CPU path (lab_4) on host cores; ms_per_step is the time a full "
+                "step of this workload would take at the sampled rate",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, tau, eps, variant):
+    return {"workload": f"{args.dist} sphere N={args.n} FP{args.precision} {args.scheme.upper()} "
+                        f"tau={tau:g} eps={eps:g} G=6.67e-11 (BASELINE.json configs[3], "
+                        f"strong scaling over --gpus)",
+            "n_bodies": args.n, "scheme": args.scheme, "tau": tau, "eps": eps,
+            "l2": "flushed between timed steps (256 MiB device write); working set 32 B/body",
+            "parallelism": (f"i-rows over {args.gpus} GPU(s), peer-pull exchange: remote j-tiles "
+                            f"fetched from the peers' HBM by the force kernel's bulk-async copies"
+                            if getattr(args, "p2p", 0) and args.gpus > 1 else
+                            f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
+                            f"per RK stage overlapped with the local-tile force launch"),
+            "kernel_variant": variant}
+
+
+# ---------------------------------------------------------------- this framework
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from parallel_comp_labs_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("NCCL_DEBUG", "WARN")   # keep stdout to the one JSON line
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run "
+                             "(--nproc-per-node N)")
+        args.gpus = world
+    torch.cuda.set_device(local)
+    uid = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        box = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    bodies, tau, eps = make_bodies(args)
+    n = args.n
+    scheme = capi.NBODY_RK4 if args.scheme == "rk4" else capi.NBODY_RK2
+    stages = 4 if args.scheme == "rk4" else 2
+    dtype = np.float64 if args.precision == 64 else np.float32
+
+    peak = capi.measure_fma_peak(args.precision, 300.0, device=local)   # roofline denominator
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    ctx = capi.Context(n, args.precision, local, rank, world, uid)
+    if args.p2p and world > 1:
+        blobs = [None] * world
+        dist.all_gather_object(blobs, ctx.p2p_export())
+        ctx.p2p_connect(blobs)
+    ctx.set_params(6.67e-11, eps)
+    ctx.set_option("variant", args.variant)
+    ctx.set_option("unimass", args.unimass)
+    host_in = capi.PinnedArray((n, 7), dtype)
+    host_out = capi.PinnedArray((n, 7), dtype)
+    host_in.array[:] = bodies.astype(dtype)
+    ctx.upload_aos(host_in.array)
+    e0 = None if args.no_energy else sum(ctx.energy())
+
+    # ---- device-resident timed region: W warm-up steps, then K timed steps ------------------
+    for _ in range(args.warmup):
+        ctx.step(scheme, tau, 1)
+    ctx.sync()
+    ctx.set_option("time_kernels", 1)
+    launches0 = ctx.timing().total_launches
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    step_ms, force_ms, force_launches = [], 0.0, 0
+    for _ in range(args.steps):
+        flush.zero_()                      # L2 flush between timed iterations (untimed)
+        torch.cuda.synchronize()
+        barrier()
+        ctx.step(scheme, tau, 1)
+        ctx.sync()
+        tm = ctx.timing()                  # CUDA events on the library's compute stream
+        step_ms.append(max_over_ranks(tm.last_call_ms))
+        force_ms += tm.force_ms
+        force_launches += tm.force_launches
+    barrier()
+    clocks = sampler.stop()
+    launches = ctx.timing().total_launches - launches0
+    ctx.set_option("time_kernels", 0)
+    total_ms = float(np.sum(step_ms))
+    value = stages * float(n) * float(n) * args.steps / (total_ms * 1e-3) / 1e9
+    e1 = None if args.no_energy else sum(ctx.energy())
+
+    # roofline of the dominant kernel (force): algorithmic flops per launch / mean duration
+    b, e = ctx.owned_range()
+    inter_per_launch = (e - b) * float(n) * stages * args.steps / max(force_launches, 1)
+    mean_force_ms = force_ms / max(force_launches, 1)
+    achieved = FLOPS_PER_INTERACTION * inter_per_launch / (mean_force_ms * 1e-3) / 1e12
+    force_share = max_over_ranks(force_ms) / total_ms
+
+    # ---- end-to-end through the public API with pinned host buffers --------------------------
+    e2e_ms = []
+    for k in range(1 + args.steps):        # first pass untimed
+        barrier()
+        t0 = time.perf_counter()
+        ctx.upload_aos(host_in.array)      # H2D of the step's input state
+        ctx.step(scheme, tau, 1)
+        ctx.download_aos(host_out.array)   # D2H of the step's result (collective gather of v)
+        dt = (time.perf_counter() - t0) * 1e3
+        if k:
+            e2e_ms.append(max_over_ranks(dt))
+    e2e_value = stages * float(n) * float(n) * len(e2e_ms) / (sum(e2e_ms) * 1e-3) / 1e9
+    bytes_io = n * 7 * np.dtype(dtype).itemsize
+    total_launches = int(sum_over_ranks(float(launches)))
+
+    line = None
+    if rank == 0:
+        variant_name = {"variant": int(tm.variant), "uniform_mass_factored_out": bool(tm.uniform_mass),
+                        "fp64_instr_per_pair": ((15 if tm.uniform_mass else 16)
+                                                - (1 if tm.variant in (5, 6) else 0))
+                        if args.precision == 64 else None}
+        line = {
+            "metric": "G body-interactions/s", "value": value, "unit": "G interactions/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64" if args.precision == 64 else "f32",
+            "data": "synthetic", "config": workload_config(args, tau, eps, variant_name),
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "G interactions/s",
+                    "h2d_bytes_per_step": int(bytes_io), "d2h_bytes_per_step": int(bytes_io),
+                    "ms_per_step": float(np.mean(e2e_ms))},
+            "gpu_launches": total_launches,
+            "roofline": {
+                "bound": "fp64_fma_pipe" if args.precision == 64 else "fp32_fma_pipe",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision)),
+                "kernel": "nbody::force_kernel", "mean_launch_ms": mean_force_ms,
+                "share_of_step": force_share,
+                "flops_per_interaction": FLOPS_PER_INTERACTION,
+                "peak_source": "measured live: nbody_measure_fma_peak (register-resident DFMA "
+                               "chains, 300 ms); MEASURED_PEAKS.json has no FP64 vector figure",
+                "frac_of_datasheet_fp64": (achieved / FP64_DATASHEET_TFLOPS
+                                           if args.precision == 64 else None),
+                "note": "compute-bound path (6e5 flop/B): neither HBM nor tensor cores bound it",
+            },
+            "pct_of_fp_peak_whole_job": 100.0 * FLOPS_PER_INTERACTION * value * 1e9 / 1e12
+                                        / (peak * world),
+            "energy_drift": (abs(e1 - e0) / abs(e0)) if e0 else None,
+        }
+    ctx.close()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        rates, info = cpu_reference_sample(bodies.astype(np.float64), eps, args.cpu_seconds)
+        line["cpu_baseline"] = dict(info, value=float(np.mean(rates)))
+    elif rank == 0:
+        line["cpu_baseline"] = None
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    host_in.free()
+    host_out.free()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
+# `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
+TRAFFIC_BYTES_PER_LAUNCH = {
+    (1 << 20, 1, 64): 61487104 + 391603968,   # profiles/r01_force_kernel_1M_ncu_full.csv
+}
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -206,10 +206,13 @@ const Variant& variant_of(const nbody_ctx* c) {
 }
 
 // j-slices per launch.  Units (i-tile, j-slice) are handed out dynamically, so the tail is
-// about one unit long: aim at >= UNITS_PER_SLOT units per resident CTA, keep a slice at
+// about half a unit long: aim at >= UNITS_PER_SLOT units per resident CTA, keep a slice at
 // least MIN_TILES tiles long (pipeline prologue + partial-sum traffic), cap the partial buffer.
+// Measured at N = 1M (tools/slices_probe.py): 6 / 12 / 20 / 32 / 64 slices = 1093 / 1103 / 1109 /
+// 1111 / 1113 G int/s, i.e. the half-unit tail model; 100 units per CTA (29 slices there) keeps
+// the tail at 0.5 % for 0.9 GB of partial sums per launch (0.1 % of the launch's HBM time).
 unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, long forced) {
-	const unsigned UNITS_PER_SLOT = 40, MIN_TILES = 2;
+	const unsigned UNITS_PER_SLOT = 100, MIN_TILES = 2;
 	unsigned smax = std::min<unsigned>(MAX_SLICES, std::max(1u, jt_count / MIN_TILES));
 	if (forced > 0) return std::min<unsigned>((unsigned)forced, std::max(1u, jt_count));
 	if (n_itiles == 0) return 1;
