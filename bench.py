@@ -361,7 +361,7 @@ def run_b200(args):
 # dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
 # `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
 TRAFFIC_BYTES_PER_LAUNCH = {
-    (1 << 20, 1, 64): 61487104 + 391603968,   # profiles/r01_force_kernel_1M_ncu_full.csv
+    (1 << 20, 1, 64): 83091968 + 963913216,   # profiles/r01_force_kernel_1M_ncu_full.csv
 }
 
 
