@@ -181,7 +181,8 @@ def run_reference(args):
 
 
 def workload_config(args, tau, eps, variant):
-    return {"workload": f"{args.dist} sphere N={args.n} FP{args.precision} {args.scheme.upper()} "
+    shape = "Plummer sphere" if args.dist == "plummer" else "uniform-random cube"
+    return {"workload": f"{shape} N={args.n} FP{args.precision} {args.scheme.upper()} "
                         f"tau={tau:g} eps={eps:g} G=6.67e-11 (BASELINE.json configs[3], "
                         f"strong scaling over --gpus)",
             "n_bodies": args.n, "scheme": args.scheme, "tau": tau, "eps": eps,
