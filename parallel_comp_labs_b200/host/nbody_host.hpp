@@ -78,17 +78,18 @@ std::vector<Body<T>> read_data(const std::string& path) {
 	if (!next(nn) || nn < 0) return bodies;
 	const std::size_t n = (std::size_t)nn;
 	bodies.reserve(n);
-	Body<T> b{};  // like operator>>, a short file leaves later records at the last value
+	// operator>> semantics on a short file (read_write_utils.hpp:27-33): fields are assigned one
+	// by one; at end of input the extraction fails without touching its field and sets failbit,
+	// after which nothing is assigned any more and every later record repeats `body`
+	// (checked against the reference build: tests/test_host_logic.py).
+	Body<T> b{};
+	bool failed = false;
 	for (std::size_t i = 0; i < n; ++i) {
-		double f[7];
-		bool ok = true;
-		for (int k = 0; k < 7 && ok; ++k) ok = next(f[k]);
-		if (ok) {
-			b.m = (T)f[0];
-			for (int k = 0; k < 3; ++k) {
-				b.r[k] = (T)f[1 + k];
-				b.v[k] = (T)f[4 + k];
-			}
+		T* field[7] = {&b.m, &b.r[0], &b.r[1], &b.r[2], &b.v[0], &b.v[1], &b.v[2]};
+		for (int k = 0; k < 7 && !failed; ++k) {
+			double f = 0;
+			if (next(f)) *field[k] = (T)f;
+			else failed = true;
 		}
 		bodies.push_back(b);
 	}

@@ -46,7 +46,8 @@ void usage() {
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
 		"           [--output-folder ../output] [--variant -1] [--report]\n"
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
-		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)");
+		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
+		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)");
 }
 
 template <typename T>
@@ -159,6 +160,15 @@ int main(int argc, char** argv) {
 		write_input_format(out, plummer ? generate_plummer(n, seed, a.num("G", 6.67e-11))
 										: generate_uniform(n, seed));
 		if (!a.has("input")) return 0;
+	}
+	if (a.has("reformat")) {  // --reformat IN --reformat-out OUT: read_data -> input format (no GPU)
+		try {
+			write_input_format(a.str("reformat-out", "/dev/stdout"),
+							   read_data<double>(a.str("reformat", "")));
+		} catch (int code) {
+			return code;
+		}
+		return 0;
 	}
 	if (a.has("lab5-sweep")) {	// lab_5's test_random_bodies() (N_body.cu:438-491): RK2, T=[0,2], tau=0.1
 		const std::string dir = a.str("lab5-sweep", "./include");

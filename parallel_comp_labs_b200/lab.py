@@ -34,10 +34,22 @@ def read_data(path: str, dtype=np.float64) -> np.ndarray:
         print("file is't open")
         raise IOError(1) from e
     n = int(tok[0])
-    vals = np.array(tok[1:1 + 7 * n], dtype=np.float64)
-    if vals.size < 7 * n:  # operator>> would leave the remaining records at the last value
-        vals = np.concatenate([vals, np.zeros(7 * n - vals.size)])
-    return vals.reshape(n, 7).astype(dtype)
+    want = 7 * n
+    vals = np.array(tok[1:1 + want], dtype=np.float64)
+    if vals.size == want:
+        return vals.reshape(n, 7).astype(dtype)
+    # short file: operator>> assigns field by field; at end of input the failing extraction
+    # leaves its field alone and nothing is assigned any more -- the partly read record keeps
+    # the previous body's remaining fields and every later record repeats it
+    out = np.zeros((n, 7))
+    k = vals.size
+    out.reshape(-1)[:k] = vals
+    rec, fld = divmod(k, 7)
+    if rec < n:
+        if rec > 0:
+            out[rec, fld:] = out[rec - 1, fld:]
+        out[rec + 1:] = out[rec]
+    return out.astype(dtype)
 
 
 def format_row(time: float, positions: np.ndarray) -> str:

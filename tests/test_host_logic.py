@@ -114,3 +114,34 @@ def test_cxx_generator_matches_python(tmp_path):
     assert np.array_equal(lab.read_data(u), generators.uniform_bodies(777))
     a, b = lab.read_data(p), generators.plummer_bodies(1500, seed=0x5EED0003)
     assert np.abs(a - b).max() / np.abs(b).max() < 1e-14
+
+
+def test_cxx_read_data_matches_python(tmp_path):
+    """The C++ host's from_chars reader accepts what operator>> accepts (tabs, CRLF, '+', exponents,
+    a short last record) and agrees with the Python mirror; --reformat needs no GPU."""
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    src = tmp_path / "in.txt"
+    src.write_bytes(b"4 \r\n8.81032e+09  -61.3392 12.7171 -99.7497 -2.99417 -0.402539 1.70019\r\n"
+                    b"1\t2\t3\t4\t\t5\t6\t7\n  +1e3 0 0 0 0 0 0\n 2.5 1 1 1")
+    out = tmp_path / "out.txt"
+    r = subprocess.run([exe, "--reformat", str(src), "--reformat-out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    a, b = lab.read_data(str(out)), lab.read_data(str(src))
+    assert a.shape == (4, 7) and np.array_equal(a[:3], b[:3])
+    assert a[2, 0] == 1000.0
+    # the truncated 4th record "2.5 1 1 1": operator>> assigns m and r and leaves v at the
+    # previous body's values (reference :27-33)
+    assert np.array_equal(a[3], [2.5, 1, 1, 1, 0, 0, 0]) and np.array_equal(a, b)
+    assert subprocess.run([exe, "--reformat", str(tmp_path / "none.txt")], capture_output=True).returncode == 1
+
+
+def test_short_file_semantics_match_reference(reflab4, tmp_path):
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    src = tmp_path / "short.txt"
+    src.write_text("5\n1 2 3 4 5 6 7\n8 9 10 11 12 13 14\n15 16 17\n")
+    want = reflab4.read_data(str(src))
+    out = tmp_path / "o.txt"
+    assert subprocess.run([exe, "--reformat", str(src), "--reformat-out", str(out)]).returncode == 0
+    assert np.array_equal(lab.read_data(str(out)), want)
+    assert np.array_equal(lab.read_data(str(src)), want)
+    assert np.array_equal(want[2], [15, 16, 17, 11, 12, 13, 14]) and np.array_equal(want[4], want[2])
