@@ -145,3 +145,21 @@ def test_short_file_semantics_match_reference(reflab4, tmp_path):
     assert np.array_equal(lab.read_data(str(out)), want)
     assert np.array_equal(lab.read_data(str(src)), want)
     assert np.array_equal(want[2], [15, 16, 17, 11, 12, 13, 14]) and np.array_equal(want[4], want[2])
+
+
+def test_cxx_number_formatting_matches_printf(reflab4, tmp_path):
+    """std::to_chars(scientific, 16) in the C++ host == the reference's iostream formatting
+    (scientific, precision 16) == printf %.16e, including 3-digit exponents, denormals, -0."""
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    vals = [1e300, -2.5e-300, 4.9e-324, -0.0, 123456789.12345679, 1.0 / 3.0, 8810324116.227]
+    src = tmp_path / "v.txt"
+    src.write_text("1\n" + " ".join(repr(x) for x in vals) + "\n")
+    out = tmp_path / "o.txt"
+    assert subprocess.run([exe, "--reformat", str(src), "--reformat-out", str(out)]).returncode == 0
+    toks = open(out).read().split()[1:]
+    assert toks == ["%.16e" % x for x in vals]
+    # and the reference's own writer on the same numbers (positions only: fields 1..3)
+    ref_csv = tmp_path / "r.csv"
+    body = np.array([vals])
+    reflab4.write_bodies_coords(str(ref_csv), vals[0], body)
+    assert open(ref_csv).read() == lab.format_row(vals[0], body[:, 1:4])
