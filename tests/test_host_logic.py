@@ -163,3 +163,25 @@ def test_cxx_number_formatting_matches_printf(reflab4, tmp_path):
     body = np.array([vals])
     reflab4.write_bodies_coords(str(ref_csv), vals[0], body)
     assert open(ref_csv).read() == lab.format_row(vals[0], body[:, 1:4])
+
+
+def test_hot_loop_instruction_budget():
+    """Regression guard on the SASS of the default FP64 force kernels (tools/sass_mix.py): the
+    hot loop has 16 FP64 instructions per pair (15 with the mass factored out), no clamp
+    compare/select, one MUFU per pair, and fewer than 4.2 other instructions per pair."""
+    import re
+    out = subprocess.run([os.sys.executable, os.path.join(ROOT, "tools", "sass_mix.py"), capi.LIB_PATH],
+                         capture_output=True, text=True).stdout
+    rows = {}
+    for line in out.splitlines():
+        m = re.match(r"double, \(int\)128, \(int\)2, \(int\)3, \(int\)8, \(int\)([01]), \(int\)8, \(int\)2 "
+                     r"loop=\s*(\d+) pairs=\s*(\d+) fp64/pair=([\d.]+) other/pair=([\d.]+)", line)
+        # the hot loop is the fully unrolled full-tile loop (16 pairs per trip); the ragged-tile
+        # loop (4 pairs) and the exact-clamp redo loop (no VIMNMX3) are off the hot path
+        if m and "VIMNMX3" in line and int(m.group(3)) == 16:
+            rows[int(m.group(1))] = (float(m.group(4)), float(m.group(5)), line)
+    assert set(rows) == {0, 1}, out[-2000:]
+    assert rows[0][0] == 16.0 and rows[1][0] == 15.0
+    for um in (0, 1):
+        assert rows[um][1] < 4.2, rows[um][2]
+        assert "'ISETP'" not in rows[um][2] and "'SEL'" not in rows[um][2], rows[um][2]
