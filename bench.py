@@ -48,6 +48,10 @@ def parse():
     ap.add_argument("--unimass", type=int, default=-1, help="-1 auto-detect equal masses, 0 off")
     ap.add_argument("--p2p", type=int, default=0,
                     help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
+    ap.add_argument("--pair-symmetry", type=int, default=0,
+                    help="1 (one GPU): evaluate each pair of distinct bodies once and credit both "
+                         "(opt-in; the default evaluates every ordered pair as the reference does)")
+    ap.add_argument("--sym-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -254,6 +258,9 @@ def run_b200(args):
     ctx.set_params(6.67e-11, eps)
     ctx.set_option("variant", args.variant)
     ctx.set_option("unimass", args.unimass)
+    if args.pair_symmetry:
+        ctx.set_option("pair_symmetry", 1)
+        ctx.set_option("sym_variant", args.sym_variant)
     host_in = capi.PinnedArray((n, 7), dtype)
     host_out = capi.PinnedArray((n, 7), dtype)
     host_in.array[:] = bodies.astype(dtype)
@@ -269,7 +276,7 @@ def run_b200(args):
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
-    step_ms, force_ms, force_launches = [], 0.0, 0
+    step_ms, force_ms, force_launches, pair_evals = [], 0.0, 0, 0
     for _ in range(args.steps):
         flush.zero_()                      # L2 flush between timed iterations (untimed)
         torch.cuda.synchronize()
@@ -280,6 +287,7 @@ def run_b200(args):
         step_ms.append(max_over_ranks(tm.last_call_ms))
         force_ms += tm.force_ms
         force_launches += tm.force_launches
+        pair_evals += tm.pair_evaluations
     barrier()
     clocks = sampler.stop()
     launches = ctx.timing().total_launches - launches0
@@ -309,6 +317,7 @@ def run_b200(args):
     e2e_value = stages * float(n) * float(n) * len(e2e_ms) / (sum(e2e_ms) * 1e-3) / 1e9
     bytes_io = n * 7 * np.dtype(dtype).itemsize
     total_launches = int(sum_over_ranks(float(launches)))
+    sum_pairs = sum_over_ranks(float(pair_evals))
 
     line = None
     if rank == 0:
@@ -316,6 +325,14 @@ def run_b200(args):
                         "fp64_instr_per_pair": ((15 if tm.uniform_mass else 16)
                                                 - (1 if tm.variant in (5, 6) else 0))
                         if args.precision == 64 else None}
+        if tm.pair_symmetry:
+            # every pair evaluation serves two interactions: 18 (20 with general masses) FP64
+            # instructions per evaluation; `value` and roofline.achieved count DELIVERED
+            # interactions (the metric's definition), roofline.evaluated_* what was computed
+            variant_name.update({"pair_symmetry": True, "sym_variant": max(args.sym_variant, 0),
+                                 "fp64_instr_per_pair": None,
+                                 "fp64_instr_per_pair_evaluation":
+                                     (18 if tm.uniform_mass else 20) if args.precision == 64 else None})
         line = {
             "metric": "G body-interactions/s", "value": value, "unit": "G interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -330,8 +347,12 @@ def run_b200(args):
             "roofline": {
                 "bound": "fp64_fma_pipe" if args.precision == 64 else "fp32_fma_pipe",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision)),
-                "kernel": "nbody::force_kernel", "mean_launch_ms": mean_force_ms,
+                "traffic": (None if tm.pair_symmetry else
+                            TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision))),
+                "kernel": "nbody::force_sym_kernel" if tm.pair_symmetry else "nbody::force_kernel",
+                "mean_launch_ms": mean_force_ms,
+                "evaluated_pairs_per_delivered_interaction":
+                    float(sum_pairs) / (stages * float(n) * float(n) * args.steps),
                 "share_of_step": force_share,
                 "flops_per_interaction": FLOPS_PER_INTERACTION,
                 "peak_source": "measured live: nbody_measure_fma_peak (register-resident DFMA "

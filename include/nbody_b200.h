@@ -50,6 +50,11 @@ typedef struct nbody_timing {
 	uint64_t steps_done;		 /* integrator steps since the last upload */
 	uint32_t uniform_mass;		 /* 1 if the uniform-mass kernels are in use (see "unimass") */
 	uint32_t variant;			 /* force-kernel variant index in use */
+	uint64_t pair_evaluations;	 /* pair evaluations the kernels actually performed in that call:
+									== interactions for the default kernels, about half of it with
+									option "pair_symmetry" (each evaluation serves both bodies) */
+	uint32_t pair_symmetry;		 /* 1 if the pair-symmetric kernels are in use */
+	uint32_t reserved_;
 } nbody_timing;
 
 /* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
@@ -98,7 +103,12 @@ int nbody_set_params(nbody_ctx* ctx, double G, double eps);
 /* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
  * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (-1 = auto: CUDA-graph replay of a step when n <= 16384 on one GPU; 0/1),
  * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
- * sum, the default; 0 = never; set before the upload). */
+ * sum, the default; 0 = never; set before the upload),
+ * "pair_symmetry" (0 = default: every ordered pair is evaluated, as the reference does; 1 =
+ * one GPU only: every pair of distinct bodies is evaluated once and credited to both bodies
+ * (Newton's third law) -- same per-pair bits, about half the arithmetic, j-side sums collected
+ * with floating-point atomics, so results are reproducible to rounding only),
+ * "sym_variant" (kernel variant id of that mode, -1 = default). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 
 /* Rows [begin,end) this rank owns (lab_4's offsets[id], counts[id],

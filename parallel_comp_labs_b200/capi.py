@@ -31,7 +31,9 @@ class Timing(C.Structure):
     _fields_ = [("last_call_ms", C.c_double), ("force_ms", C.c_double),
                 ("force_launches", C.c_uint64), ("total_launches", C.c_uint64),
                 ("interactions", C.c_uint64), ("steps_done", C.c_uint64),
-                ("uniform_mass", C.c_uint32), ("variant", C.c_uint32)]
+                ("uniform_mass", C.c_uint32), ("variant", C.c_uint32),
+                ("pair_evaluations", C.c_uint64), ("pair_symmetry", C.c_uint32),
+                ("reserved_", C.c_uint32)]
 
 
 def build_library(quiet: bool = True) -> None:

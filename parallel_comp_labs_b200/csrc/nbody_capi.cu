@@ -20,6 +20,7 @@
 
 #include "../../include/nbody_b200.h"
 #include "force_kernels.cuh"
+#include "force_sym_kernels.cuh"
 #include "stage_kernels.cuh"
 
 using namespace nbody;
@@ -115,6 +116,40 @@ const Variant g_var32[] = {
 	NB_VARIANT(float, 128, 8, 3, 4, 4, 2),
 	NB_VARIANT(float, 256, 4, 3, 2, 4, 2),
 };
+
+// Pair-symmetric kernels (force_sym_kernels.cuh), opt-in with option "pair_symmetry".
+struct SymVariant {
+	int threads, ipt;
+	size_t smem;
+	const void* fn[2];	// [0] general masses, [1] uniform mass factored out
+	void (*launch[2])(dim3, cudaStream_t, size_t, const SymParams&, double eps2);
+	const char* name;
+};
+template <typename T, int TH, int I, int ST, int MB, int UM, int ORD>
+void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p, double eps2) {
+	force_sym_kernel<T, TH, I, ST, MB, UM, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
+}
+#define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD)                                                  \
+	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
+				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD>,                      \
+				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD>},                     \
+				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD>, launch_force_sym<T, TH, I, ST, MB, 1, ORD>}, \
+				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD }
+// {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order}
+const SymVariant g_sym64[] = {
+	NB_SYM_VARIANT(double, 128, 4, 2, 5, 2),  // 96 registers, 20 warps/SM
+	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2),  // 128 registers, 16 warps/SM
+	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2),
+	NB_SYM_VARIANT(double, 128, 2, 2, 8, 2),
+	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2),
+};
+const SymVariant g_sym32[] = {
+	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2),
+	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2),
+};
+constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
+constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);
+constexpr unsigned SYM_EXTRA_TILES = 4;	 // rows allocated past n_pad: phantom tiles of the last block
 constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
 constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
 constexpr unsigned PAD_UNIT = 256;	 // == TJ: per-rank blocks are whole j-tiles
@@ -131,6 +166,12 @@ struct nbody_ctx {
 		 *acc_v = nullptr, *apart = nullptr, *rhs_out = nullptr, *vel_all = nullptr,
 		 *d_aos = nullptr;
 	unsigned apart_slices = 0;
+	size_t apart_bytes = 0;
+	void* aj = nullptr;		 // T[3][aj_rows] j-side sums of the pair-symmetric kernel
+	unsigned aj_rows = 0;
+	long opt_pair_symmetry = 0, opt_sym_variant = -1;
+	uint64_t sym_pairs = 0;	 // pair evaluations of one symmetric RHS (cached with its key)
+	int sym_pairs_key = -1;
 	double* d_energy = nullptr;
 	unsigned* d_counters = nullptr;	 // work-unit ticket counters (one per force launch of a stage)
 	void* snap_dev[NBODY_SNAPSHOT_SLOTS] = {};
@@ -205,6 +246,14 @@ const Variant& variant_of(const nbody_ctx* c) {
 	return tab[v];
 }
 
+const SymVariant& sym_variant_of(const nbody_ctx* c) {
+	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
+	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
+	long v = c->opt_sym_variant;
+	if (v < 0 || v >= nv) v = 0;
+	return tab[v];
+}
+
 // j-slices per launch.  Units (i-tile, j-slice) are handed out dynamically, so the tail is
 // about half a unit long: aim at >= UNITS_PER_SLOT units per resident CTA, keep a slice at
 // least MIN_TILES tiles long (pipeline prologue + partial-sum traffic), cap the partial buffer.
@@ -224,23 +273,97 @@ unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, lon
 // ------------------------------------------------------------------ helpers on a context
 namespace {
 
-int ensure_apart(nbody_ctx* ctx, unsigned slices) {
-	if (slices <= ctx->apart_slices) return NBODY_OK;
-	CK(cudaStreamSynchronize(ctx->sc));
-	if (ctx->apart) CK(cudaFree(ctx->apart));
-	ctx->apart = nullptr;
-	CK(cudaMalloc(&ctx->apart, (size_t)slices * ctx->own_pad * 4 * ctx->esz));
-	ctx->apart_slices = slices;
-	return NBODY_OK;
-}
-
 struct LaunchPlan {
 	unsigned n_itiles, slots, grid;
 	unsigned s_local, s_remote;	 // slices
 	unsigned jt_total, jt_per_rank;
+	unsigned apart_stride;	// rows between slices of apart
+	// pair-symmetric kernel (one GPU): blocks of tpb j-tiles, s_local slices of a block's walk
+	bool sym;
+	unsigned nb, tpb, rows_pad;
 };
 
+int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
+	const size_t bytes = (size_t)(lp.s_local + lp.s_remote) * lp.apart_stride * 4 * ctx->esz;
+	if (bytes > ctx->apart_bytes) {
+		CK(cudaStreamSynchronize(ctx->sc));
+		if (ctx->apart) CK(cudaFree(ctx->apart));
+		ctx->apart = nullptr;
+		ctx->apart_bytes = 0;
+		CK(cudaMalloc(&ctx->apart, bytes));
+		ctx->apart_bytes = bytes;
+	}
+	ctx->apart_slices = lp.s_local + lp.s_remote;
+	if (lp.sym && lp.rows_pad > ctx->aj_rows) {
+		CK(cudaStreamSynchronize(ctx->sc));
+		if (ctx->aj) CK(cudaFree(ctx->aj));
+		ctx->aj = nullptr;
+		ctx->aj_rows = 0;
+		CK(cudaMalloc(&ctx->aj, (size_t)3 * lp.rows_pad * ctx->esz));
+		ctx->aj_rows = lp.rows_pad;
+	}
+	return NBODY_OK;
+}
+
+// pair evaluations of one pair-symmetric RHS: block rows x the j-bodies their walk touches
+// (whole strips of 32 in partner tiles, existing bodies in the block's own tiles)
+uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb) {
+	const unsigned TJ = 256, block = tpb * TJ;
+	std::vector<uint64_t> own(nb), strips(nb + 1, 0);  // strips: prefix sums over blocks
+	for (unsigned b = 0; b < nb; ++b) {
+		uint64_t o = 0, st = 0;
+		for (unsigned q = 0; q < tpb; ++q) {
+			const uint64_t first = (uint64_t)(b * tpb + q) * TJ;
+			const uint64_t cnt = first >= n_real ? 0 : std::min<uint64_t>(TJ, n_real - first);
+			o += cnt;
+			st += (cnt + 31) / 32 * 32;
+		}
+		own[b] = o;
+		strips[b + 1] = strips[b] + st;
+	}
+	uint64_t total = 0;
+	for (unsigned a = 0; a < nb; ++a) {
+		const unsigned h = sym_half(nb, a);
+		const unsigned lo = a + 1, hi = a + 1 + h;	// partner blocks [lo,hi) cyclic
+		uint64_t part = hi <= nb ? strips[hi] - strips[lo]
+								 : (strips[nb] - strips[std::min(lo, nb)]) + strips[hi - nb];
+		total += (uint64_t)block * (own[a] + part);
+	}
+	return total;
+}
+
 int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
+	lp->sym = ctx->opt_pair_symmetry != 0;
+	if (lp->sym) {
+		if (ctx->world > 1)
+			return fail(ctx, NBODY_ERR_STATE, "option \"pair_symmetry\" needs a single-GPU context");
+		const SymVariant& sv = sym_variant_of(ctx);
+		const unsigned TJ = 256, block = sv.threads * sv.ipt;
+		lp->tpb = block / TJ;
+		lp->jt_total = ctx->n_pad / TJ;
+		lp->jt_per_rank = lp->jt_total;
+		lp->nb = (lp->jt_total + lp->tpb - 1) / lp->tpb;
+		lp->rows_pad = lp->nb * block;
+		lp->apart_stride = lp->rows_pad;
+		lp->n_itiles = lp->nb;
+		int per_sm = 0;
+		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sv.fn[ctx->unimass ? 1 : 0],
+														sv.threads, sv.smem));
+		if (per_sm < 1) return fail(ctx, NBODY_ERR_CUDA, "force kernel does not fit on an SM");
+		lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
+		// shortest walk of a block: tpb * (1 + h) tiles with h >= (nb-1)/2 - (nb even ? 0 : 0)
+		const unsigned min_walk = sym_ntiles(lp->nb, lp->tpb, lp->nb - 1);
+		lp->s_local = choose_slices(lp->nb, min_walk, lp->slots, ctx->opt_slices);
+		lp->s_remote = 0;
+		const int key = (int)(sv.threads * sv.ipt);
+		if (ctx->sym_pairs_key != key) {
+			ctx->sym_pairs = sym_pair_evaluations((unsigned)ctx->n, lp->nb, lp->tpb);
+			ctx->sym_pairs_key = key;
+		}
+		return NBODY_OK;
+	}
+	lp->nb = lp->tpb = lp->rows_pad = 0;
+	lp->apart_stride = ctx->own_pad;
 	const Variant& v = variant_of(ctx);
 	const unsigned itile = v.threads * v.ipt;
 	const unsigned TJ = 256;
@@ -324,6 +447,46 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 	return NBODY_OK;
 }
 
+// one pair-symmetric force launch over all bodies of `buf` (single GPU)
+int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
+	const SymVariant& v = sym_variant_of(ctx);
+	SymParams p;
+	p.pos = buf_ptr(ctx, buf);
+	p.apart = ctx->apart;
+	p.aj = ctx->aj;
+	p.rows_pad = lp.rows_pad;
+	p.nb = lp.nb;
+	p.jt_total = lp.jt_total;
+	p.n_pad = ctx->n_pad;
+	p.n_real = (unsigned)ctx->n;
+	p.n_slices = lp.s_local;
+	p.counter = ctx->d_counters;
+	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
+	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
+	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
+	const unsigned long long units = (unsigned long long)lp.nb * lp.s_local;
+	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
+	cudaEvent_t e0 = nullptr, e1 = nullptr;
+	if (ctx->opt_time_kernels) {
+		if (ctx->kev_used + 2 > ctx->kev.size()) {
+			for (int k = 0; k < 2; ++k) {
+				cudaEvent_t e;
+				CK(cudaEventCreate(&e));
+				ctx->kev.push_back(e);
+			}
+		}
+		e0 = ctx->kev[ctx->kev_used++];
+		e1 = ctx->kev[ctx->kev_used++];
+		CK(cudaEventRecord(e0, ctx->sc));
+	}
+	v.launch[ctx->unimass ? 1 : 0](dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
+	CK(cudaGetLastError());
+	if (e1) CK(cudaEventRecord(e1, ctx->sc));
+	ctx->tm.force_launches++;
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+
 // all-gather the owned block of `buf` (V4[n_pad]) across ranks on the comm stream,
 // after everything enqueued so far on sc; leaves `done` recorded on sm.
 int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
@@ -365,6 +528,11 @@ int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, GatherMod
 	int rc;
 	ctx->tm.interactions += (uint64_t)ctx->own_real * (uint64_t)ctx->n;	 // self pairs counted,
 	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
+	if (lp.sym) {
+		ctx->tm.pair_evaluations += ctx->sym_pairs;
+		return launch_force_sym_all(ctx, lp, buf);
+	}
+	ctx->tm.pair_evaluations += (uint64_t)ctx->own_real * (uint64_t)ctx->n;
 	if (ctx->world == 1)
 		return launch_force_range(ctx, lp, buf, false, 0, lp.jt_total, lp.s_local, 0);
 	if (!ctx->p2p && mode == GATHER_NOW && (rc = enqueue_gather(ctx, buf_ptr(ctx, buf), ctx->e_g)))
@@ -403,6 +571,9 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	p.own_pad = ctx->own_pad;
 	p.own_real = ctx->own_real;
 	p.n_slices = lp.s_local + lp.s_remote;
+	p.apart_stride = lp.apart_stride;
+	p.aj = lp.sym ? ctx->aj : nullptr;
+	p.aj_stride = lp.rows_pad;
 	p.mass_scale = ctx->unimass ? (T)ctx->uniform_mass : T(1);
 	p.minusG = (T)(-(T)ctx->G);
 	p.c_next = (T)c_next;
@@ -531,7 +702,7 @@ void nbody_destroy(nbody_ctx* ctx) {
 		}
 	if (ctx->comm && g_nccl.lib) g_nccl.CommDestroy(ctx->comm);
 	void* bufs[] = {ctx->Y, ctx->P, ctx->vel_n, ctx->vel_s, ctx->acc_r, ctx->acc_v, ctx->apart,
-					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters,
+					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters, ctx->aj,
 					ctx->P2, ctx->d_flags, ctx->d_peer_flags};
 	for (void* b : bufs)
 		if (b) cudaFree(b);
@@ -575,8 +746,13 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 	CK(cudaEventCreate(&ctx->ev_start));
 	CK(cudaEventCreate(&ctx->ev_stop));
 	const size_t v4 = 4 * ctx->esz;
-	CK(cudaMalloc(&ctx->Y, (size_t)ctx->n_pad * v4));
-	CK(cudaMalloc(&ctx->P, (size_t)ctx->n_pad * v4));
+	// SYM_EXTRA_TILES tiles past n_pad: the last block of the pair-symmetric walk may name tiles
+	// that hold no bodies; they are fetched (and ignored), so they must be mapped
+	const size_t pos_rows = (size_t)ctx->n_pad + SYM_EXTRA_TILES * PAD_UNIT;
+	CK(cudaMalloc(&ctx->Y, pos_rows * v4));
+	CK(cudaMalloc(&ctx->P, pos_rows * v4));
+	CK(cudaMemset((char*)ctx->Y + (size_t)ctx->n_pad * v4, 0, SYM_EXTRA_TILES * PAD_UNIT * v4));
+	CK(cudaMemset((char*)ctx->P + (size_t)ctx->n_pad * v4, 0, SYM_EXTRA_TILES * PAD_UNIT * v4));
 	CK(cudaMalloc(&ctx->vel_n, (size_t)ctx->own_pad * v4));
 	CK(cudaMalloc(&ctx->vel_s, (size_t)ctx->own_pad * v4));
 	CK(cudaMalloc(&ctx->acc_r, (size_t)ctx->own_pad * v4));
@@ -591,6 +767,12 @@ static int create_impl(nbody_ctx* ctx, const void* nccl_uid) {
 		for (int i = 0; i < N_VAR32; ++i)
 			CK(cudaFuncSetAttribute(g_var32[i].fn[u], cudaFuncAttributeMaxDynamicSharedMemorySize,
 									(int)g_var32[i].smem));
+		for (int i = 0; i < N_SYM64; ++i)
+			CK(cudaFuncSetAttribute(g_sym64[i].fn[u], cudaFuncAttributeMaxDynamicSharedMemorySize,
+									(int)g_sym64[i].smem));
+		for (int i = 0; i < N_SYM32; ++i)
+			CK(cudaFuncSetAttribute(g_sym32[i].fn[u], cudaFuncAttributeMaxDynamicSharedMemorySize,
+									(int)g_sym32[i].smem));
 	}
 	if (ctx->world > 1) {
 		if (ctx->world <= 8) {	// buffers the peer-pull exchange exports (nbody_p2p_export)
@@ -728,6 +910,15 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "variant out of range");
 		ctx->opt_variant = value;
 	} else if (k == "use_graph") ctx->opt_use_graph = value;
+	else if (k == "pair_symmetry") {
+		if (value != 0 && ctx->world > 1)
+			return fail(ctx, NBODY_ERR_STATE, "option \"pair_symmetry\" needs a single-GPU context");
+		ctx->opt_pair_symmetry = value != 0;
+	} else if (k == "sym_variant") {
+		const int nv = ctx->prec == 64 ? N_SYM64 : N_SYM32;
+		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "sym_variant out of range");
+		ctx->opt_sym_variant = value;
+	}
 	else if (k == "unimass") {
 		if (ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "set \"unimass\" before the upload");
 		ctx->opt_unimass = value;
@@ -838,6 +1029,7 @@ int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* 
 static int begin_timed_call(nbody_ctx* ctx) {
 	ctx->tm.force_launches = 0;
 	ctx->tm.interactions = 0;
+	ctx->tm.pair_evaluations = 0;
 	ctx->tm.force_ms = 0;
 	ctx->kev_used = 0;
 	CK(cudaEventRecord(ctx->ev_start, ctx->sc));
@@ -856,7 +1048,7 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 	LaunchPlan lp;
 	int rc;
 	if ((rc = make_plan(ctx, &lp))) return rc;
-	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
+	if ((rc = ensure_apart(ctx, lp))) return rc;
 	if (!ctx->rhs_out) CK(cudaMalloc(&ctx->rhs_out, (size_t)ctx->own_pad * 3 * ctx->esz));
 	if ((rc = begin_timed_call(ctx))) return rc;
 	if ((rc = enqueue_forces(ctx, lp, BUF_Y, ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE)))
@@ -877,7 +1069,7 @@ static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double ta
 	LaunchPlan lp;
 	int rc;
 	if ((rc = make_plan(ctx, &lp))) return rc;
-	if ((rc = ensure_apart(ctx, lp.s_local + lp.s_remote))) return rc;
+	if ((rc = ensure_apart(ctx, lp))) return rc;
 	if ((rc = begin_timed_call(ctx))) return rc;
 	long done = 0;
 	// Launch-bound regime (small n, single rank): replay one captured step as a CUDA graph
@@ -905,6 +1097,8 @@ static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double ta
 			ctx->tm.force_launches += k.ns;
 			ctx->tm.total_launches += 2 * k.ns;
 			ctx->tm.interactions += (uint64_t)k.ns * ctx->own_real * ctx->n;
+			ctx->tm.pair_evaluations +=
+				(uint64_t)k.ns * (lp.sym ? ctx->sym_pairs : (uint64_t)ctx->own_real * ctx->n);
 		}
 	}
 	for (; done < n_steps; ++done)
@@ -964,6 +1158,7 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 		ctx->timing_pending = false;
 	}
 	ctx->tm.uniform_mass = ctx->unimass ? 1u : 0u;
+	ctx->tm.pair_symmetry = ctx->opt_pair_symmetry ? 1u : 0u;
 	{
 		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;
 		ctx->tm.variant = (ctx->opt_variant < 0 || ctx->opt_variant >= nv) ? 0u : (uint32_t)ctx->opt_variant;

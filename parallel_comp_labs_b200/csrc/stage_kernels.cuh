@@ -32,6 +32,9 @@ struct StageParams {
 	void* acc_v;		// V4[own_pad]                    (velocities part)
 	void* rhs_out;		// optional T[3*own_real]: -G*sum only (nbody_rhs test hook)
 	unsigned own0, own_pad, own_real, n_slices;
+	unsigned apart_stride;	// rows between consecutive slices of apart (own_pad for K1)
+	const void* aj;			// optional T[3][aj_stride]: j-side sums of the pair-symmetric kernel
+	unsigned aj_stride;
 	T mass_scale;	 // the uniform mass factored out of K1 (1 when masses differ: exact no-op)
 	T minusG;		 // -G
 	T c_next;		 // a_{s+1,s} * tau (tau/2, tau/2, tau for RK4; tau/2 for RK2)
@@ -49,10 +52,16 @@ __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
 	// fixed-order slice reduction, then a *= -G (struct_ode_system.hpp:73)
 	T ax = T(0), ay = T(0), az = T(0);
 	for (unsigned s = 0; s < p.n_slices; ++s) {
-		const vec4 q = apart[(size_t)s * p.own_pad + i];
+		const vec4 q = apart[(size_t)s * p.apart_stride + i];
 		ax = add_rn(ax, q.x);
 		ay = add_rn(ay, q.y);
 		az = add_rn(az, q.z);
+	}
+	if (p.aj) {	 // reactions collected by force_sym_kernel (global row index)
+		const T* g = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
+		ax = add_rn(ax, g[0]);
+		ay = add_rn(ay, g[(size_t)p.aj_stride]);
+		az = add_rn(az, g[2 * (size_t)p.aj_stride]);
 	}
 	ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
 	ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);

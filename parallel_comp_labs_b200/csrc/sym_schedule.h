@@ -1,0 +1,53 @@
+// sym_schedule.h -- work decomposition of the pair-symmetric force kernel (force_sym_kernels.cuh).
+//
+// Plain integer arithmetic shared by the device kernel, the host planner (nbody_capi.cu) and the
+// CPU coverage test (tests/tools/sym_coverage.cpp), so that what the test proves is what the
+// kernel walks.
+//
+// The bodies are cut into `nb` blocks of `tpb` j-tiles (one block == the i-rows of one CTA).
+// Block a meets
+//   * itself, one-sided (every ordered pair inside the block, self pairs included), and
+//   * the next h(a) blocks in cyclic order, symmetrically: every pair (i in a, j in b) is
+//     evaluated once and credited to both bodies (Newton's third law).
+// With h(a) = (nb-1)/2 for odd nb, and nb/2 (a < nb/2) or nb/2-1 (a >= nb/2) for even nb, every
+// unordered pair of distinct blocks is met exactly once, and every block does the same amount of
+// work up to one partner block.
+#pragma once
+
+#if defined(__CUDACC__)
+#define NB_HD __host__ __device__ __forceinline__
+#else
+#define NB_HD inline
+#endif
+
+namespace nbody {
+
+// number of partner blocks of block a
+NB_HD unsigned sym_half(unsigned nb, unsigned a) {
+	if (nb & 1u) return (nb - 1u) / 2u;
+	return a < nb / 2u ? nb / 2u : nb / 2u - 1u;
+}
+
+// j-tiles block a walks: tpb diagonal tiles first, then tpb per partner block
+NB_HD unsigned sym_ntiles(unsigned nb, unsigned tpb, unsigned a) {
+	return tpb * (1u + sym_half(nb, a));
+}
+
+// q-th tile of block a's walk (absolute tile index; may be a phantom tile >= jt_total when the
+// last block is incomplete -- such tiles hold no bodies).  *diag = tile of the block itself.
+NB_HD unsigned sym_tile(unsigned nb, unsigned tpb, unsigned a, unsigned q, bool* diag) {
+	*diag = q < tpb;
+	if (q < tpb) return a * tpb + q;
+	const unsigned step = (q - tpb) / tpb;	// 0 .. h-1
+	unsigned b = a + 1u + step;
+	if (b >= nb) b -= nb;
+	return b * tpb + (q - tpb) % tpb;
+}
+
+// tiles [t0,t1) of the walk that slice s of S takes
+NB_HD void sym_slice_range(unsigned ntiles, unsigned S, unsigned s, unsigned* t0, unsigned* t1) {
+	*t0 = (unsigned)(((unsigned long long)s * ntiles) / S);
+	*t1 = (unsigned)(((unsigned long long)(s + 1u) * ntiles) / S);
+}
+
+}  // namespace nbody
