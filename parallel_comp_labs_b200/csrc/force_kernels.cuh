@@ -26,7 +26,12 @@
 //    all masses are equal and the mass is factored out (UM);
 //  * FP32: MUFU.RSQ directly (tolerance 1e-4), 13-14 FP32 issue slots per pair.
 #pragma once
+// NBODY_HOST_EMU: tests/tools/cuda_emu.h runs these kernels lane by lane on the CPU (test
+// infrastructure; it supplies the CUDA vocabulary and the PTX helpers below as plain C++).
+#ifndef NBODY_HOST_EMU
 #include <cuda_runtime.h>
+#define NB_DYN_SMEM(name) extern __shared__ __align__(128) unsigned char name[]
+#endif
 #include <stdint.h>
 
 namespace nbody {
@@ -36,6 +41,7 @@ template <> struct V4<double> { typedef double4 type; };
 template <> struct V4<float> { typedef float4 type; };
 
 // ---------------------------------------------------------------- PTX helpers
+#ifndef NBODY_HOST_EMU
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 	return (uint32_t)__cvta_generic_to_shared(p);
 }
@@ -85,6 +91,7 @@ __device__ __forceinline__ float rsqrt_seed(float x) {
 	asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
 	return y;
 }
+#endif	// !NBODY_HOST_EMU
 
 // Clamp constants prepared on the host.  key(r2) is an int that orders like r2 for r2 >= +0
 // (FP64: the high word; FP32: the bit pattern); "key(r2) <= thresh" is a conservative test
@@ -241,7 +248,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	constexpr int TJ = Tile<T>::TJ;
 	constexpr uint32_t TILE_BYTES = TJ * sizeof(vec4);
 
-	extern __shared__ __align__(128) unsigned char smem_raw[];
+	NB_DYN_SMEM(smem_raw);
 	vec4* tiles = reinterpret_cast<vec4*>(smem_raw);
 	uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STAGES * TILE_BYTES);
 	volatile unsigned* next_unit_s = reinterpret_cast<volatile unsigned*>(full + STAGES);

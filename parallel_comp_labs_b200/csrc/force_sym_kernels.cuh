@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	constexpr uint32_t TILE_BYTES = TJ * sizeof(vec4);
 	constexpr size_t ACC_BYTES = (size_t)3 * I * THREADS * sizeof(T);
 
-	extern __shared__ __align__(128) unsigned char smem_raw[];
+	NB_DYN_SMEM(smem_raw);
 	vec4* tiles = reinterpret_cast<vec4*>(smem_raw);
 	T* accm = reinterpret_cast<T*>(smem_raw + (size_t)STAGES * TILE_BYTES);	 // [3*I][THREADS]
 	uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)STAGES * TILE_BYTES + ACC_BYTES);

@@ -9,7 +9,9 @@
 // contraction): for RK2 this reproduces the reference's stage arithmetic bit-for-bit
 // given the same accelerations.
 #pragma once
+#ifndef NBODY_HOST_EMU
 #include <cuda_runtime.h>
+#endif
 #include <stdint.h>
 
 #include "force_kernels.cuh"
@@ -307,6 +309,7 @@ __global__ void __launch_bounds__(256)
 // same stream) it publishes the production epoch into every peer's flag array; a peer's remote
 // force launch is preceded by p2p_wait on the epochs it needs.  One launch per GPU, different
 // GPUs: no two waiting kernels ever share a device.
+#ifndef NBODY_HOST_EMU
 __global__ void p2p_signal_kernel(unsigned* const* peer_flags, int world, int rank, unsigned epoch) {
 	const int p = threadIdx.x;
 	if (p < world && p != rank) {
@@ -325,6 +328,8 @@ __global__ void p2p_wait_kernel(const unsigned* flags, int world, int rank, unsi
 		} while ((int)(v - epoch) < 0);
 	}
 }
+
+#endif  // !NBODY_HOST_EMU
 
 // FMA-pipe peak microbenchmark: 8 independent dependent-chains per thread, register
 // resident, no memory traffic.  flops = 2 * 8 * iters * threads.
