@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--p2p", type=int, default=0,
                     help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
     ap.add_argument("--pair-symmetry", type=int, default=0,
-                    help="1 (one GPU): evaluate each pair of distinct bodies once and credit both "
+                    help="1: evaluate each pair of distinct bodies once and credit both "
                          "(opt-in; the default evaluates every ordered pair as the reference does)")
     ap.add_argument("--sym-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")

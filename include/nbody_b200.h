@@ -105,9 +105,11 @@ int nbody_set_params(nbody_ctx* ctx, double G, double eps);
  * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
  * sum, the default; 0 = never; set before the upload),
  * "pair_symmetry" (0 = default: every ordered pair is evaluated, as the reference does; 1 =
- * one GPU only: every pair of distinct bodies is evaluated once and credited to both bodies
- * (Newton's third law) -- same per-pair bits, about half the arithmetic, j-side sums collected
- * with floating-point atomics, so results are reproducible to rounding only),
+ * every pair of distinct bodies is evaluated once and credited to both bodies (Newton's third
+ * law) -- same per-pair bits, about half the arithmetic; j-side sums are collected with
+ * floating-point atomics, so results are reproducible to rounding only; on several GPUs the
+ * ranks split the blocks of one global schedule and the j-side sums are reduce-scattered
+ * (needs the per-rank block of nbody_partition to be a multiple of 512 rows, NCCL exchange)),
  * "sym_variant" (kernel variant id of that mode, -1 = default). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 

@@ -35,10 +35,12 @@ namespace nbody {
 
 struct SymParams {
 	const void* pos;	 // V4[(jt_total + tpb) * TJ] positions {x,y,z,m}; rows >= n_pad unspecified
-	void* apart;		 // V4[n_slices][rows_pad] i-side partial sums (w unused)
-	void* aj;			 // T[3][rows_pad] j-side sums, zeroed before the launch
-	unsigned rows_pad;	 // nb * THREADS * I
-	unsigned nb;		 // blocks
+	void* apart;		 // V4[n_slices][nb_own * BLOCK] i-side partial sums of the owned blocks
+	void* aj;			 // T[3][rows_pad] j-side sums (global row index), zeroed before the launch
+	unsigned rows_pad;	 // nb * BLOCK, BLOCK = THREADS * I
+	unsigned nb;		 // blocks of the whole problem
+	unsigned block0;	 // first block this GPU owns (multi-GPU: the ranks split the blocks, every
+	unsigned nb_own;	 //   rank walks the same global schedule, j-side sums are reduce-scattered)
 	unsigned jt_total;	 // tiles that exist (n_pad / TJ)
 	unsigned n_pad;		 // rows of pos that are initialised (real bodies + pad bodies)
 	unsigned n_real;	 // bodies that exist
@@ -146,14 +148,16 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	__syncthreads();
 
 	uint32_t ring = 0;	// tiles consumed so far by this CTA
-	const unsigned n_units = p.nb * p.n_slices;
+	const unsigned n_units = p.nb_own * p.n_slices;
+	const size_t apart_stride = (size_t)p.nb_own * BLOCK;
 
 	unsigned unit = blockIdx.x;
 	while (unit < n_units) {
 		unsigned next_ticket = 0;
 		if (tid == 0) next_ticket = gridDim.x + atomicAdd(p.counter, 1u);  // consumed at the end
-		const unsigned a = unit / p.n_slices;
-		const unsigned slice = unit - a * p.n_slices;
+		const unsigned a_loc = unit / p.n_slices;
+		const unsigned slice = unit - a_loc * p.n_slices;
+		const unsigned a = p.block0 + a_loc;
 		unsigned t0, t1;
 		sym_slice_range(sym_ntiles(p.nb, TPB, a), p.n_slices, slice, &t0, &t1);
 		const unsigned ntiles = t1 - t0;
@@ -244,7 +248,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			}
 		}
 
-		vec4* out = apart + (size_t)slice * p.rows_pad;
+		vec4* out = apart + (size_t)slice * apart_stride + (size_t)a_loc * BLOCK + tid;
 #pragma unroll
 		for (int k = 0; k < I; ++k) {
 			vec4 o;
@@ -252,7 +256,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			o.y = accm[(1 * I + k) * THREADS + tid];
 			o.z = accm[(2 * I + k) * THREADS + tid];
 			o.w = T(0);
-			out[row0 + k * THREADS] = o;  // row < rows_pad always
+			out[k * THREADS] = o;
 		}
 		if (tid == 0) *next_unit_s = next_ticket;
 		__syncthreads();

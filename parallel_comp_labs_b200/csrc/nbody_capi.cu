@@ -30,7 +30,7 @@ namespace {
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-enum { NCCL_INT8 = 0, NCCL_DOUBLE = 8, NCCL_SUM = 0 };
+enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0 };
 struct NcclApi {
 	void* lib = nullptr;
 	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
@@ -38,6 +38,9 @@ struct NcclApi {
 	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
 	ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
 	ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*ReduceScatter)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*GroupStart)() = nullptr;
+	ncclResult_t (*GroupEnd)() = nullptr;
 	const char* (*GetErrorString)(ncclResult_t) = nullptr;
 	std::string err;
 	std::mutex mu;
@@ -57,7 +60,7 @@ struct NcclApi {
 		}
 #define NB_SYM(f) *(void**)(&f) = dlsym(lib, "nccl" #f); if (!f) { err = "missing nccl" #f; lib = nullptr; return false; }
 		NB_SYM(GetUniqueId) NB_SYM(CommInitRank) NB_SYM(CommDestroy) NB_SYM(AllGather)
-		NB_SYM(AllReduce) NB_SYM(GetErrorString)
+		NB_SYM(AllReduce) NB_SYM(ReduceScatter) NB_SYM(GroupStart) NB_SYM(GroupEnd) NB_SYM(GetErrorString)
 #undef NB_SYM
 		return true;
 	}
@@ -280,7 +283,8 @@ struct LaunchPlan {
 	unsigned apart_stride;	// rows between slices of apart
 	// pair-symmetric kernel (one GPU): blocks of tpb j-tiles, s_local slices of a block's walk
 	bool sym;
-	unsigned nb, tpb, rows_pad;
+	unsigned nb, tpb, rows_pad;	 // blocks of the whole problem, tiles per block, nb * block rows
+	unsigned block0, nb_own;	 // blocks this rank owns
 };
 
 int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
@@ -307,7 +311,8 @@ int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
 
 // pair evaluations of one pair-symmetric RHS: block rows x the j-bodies their walk touches
 // (whole strips of 32 in partner tiles, existing bodies in the block's own tiles)
-uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb) {
+uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb, unsigned block0,
+							  unsigned nb_own) {
 	const unsigned TJ = 256, block = tpb * TJ;
 	std::vector<uint64_t> own(nb), strips(nb + 1, 0);  // strips: prefix sums over blocks
 	for (unsigned b = 0; b < nb; ++b) {
@@ -322,7 +327,7 @@ uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb) {
 		strips[b + 1] = strips[b] + st;
 	}
 	uint64_t total = 0;
-	for (unsigned a = 0; a < nb; ++a) {
+	for (unsigned a = block0; a < block0 + nb_own; ++a) {
 		const unsigned h = sym_half(nb, a);
 		const unsigned lo = a + 1, hi = a + 1 + h;	// partner blocks [lo,hi) cyclic
 		uint64_t part = hi <= nb ? strips[hi] - strips[lo]
@@ -335,17 +340,25 @@ uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb) {
 int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 	lp->sym = ctx->opt_pair_symmetry != 0;
 	if (lp->sym) {
-		if (ctx->world > 1)
-			return fail(ctx, NBODY_ERR_STATE, "option \"pair_symmetry\" needs a single-GPU context");
 		const SymVariant& sv = sym_variant_of(ctx);
 		const unsigned TJ = 256, block = sv.threads * sv.ipt;
+		if (ctx->world > 1 && ctx->p2p)
+			return fail(ctx, NBODY_ERR_STATE,
+						"option \"pair_symmetry\" is not available with the peer-pull exchange");
+		if (ctx->world > 1 && ctx->own_pad % block)
+			return fail(ctx, NBODY_ERR_STATE,
+						"option \"pair_symmetry\" on several GPUs needs the per-rank block (" +
+							std::to_string(ctx->own_pad) + " rows) to be a multiple of " +
+							std::to_string(block) + " rows");
 		lp->tpb = block / TJ;
 		lp->jt_total = ctx->n_pad / TJ;
-		lp->jt_per_rank = lp->jt_total;
+		lp->jt_per_rank = ctx->own_pad / TJ;
 		lp->nb = (lp->jt_total + lp->tpb - 1) / lp->tpb;
 		lp->rows_pad = lp->nb * block;
-		lp->apart_stride = lp->rows_pad;
-		lp->n_itiles = lp->nb;
+		lp->nb_own = ctx->world > 1 ? ctx->own_pad / block : lp->nb;
+		lp->block0 = (unsigned)ctx->rank * (ctx->world > 1 ? lp->nb_own : 0u);
+		lp->apart_stride = lp->nb_own * block;
+		lp->n_itiles = lp->nb_own;
 		int per_sm = 0;
 		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sv.fn[ctx->unimass ? 1 : 0],
 														sv.threads, sv.smem));
@@ -353,16 +366,16 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 		lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
 		// shortest walk of a block: tpb * (1 + h) tiles with h >= (nb-1)/2 - (nb even ? 0 : 0)
 		const unsigned min_walk = sym_ntiles(lp->nb, lp->tpb, lp->nb - 1);
-		lp->s_local = choose_slices(lp->nb, min_walk, lp->slots, ctx->opt_slices);
+		lp->s_local = choose_slices(lp->nb_own, min_walk, lp->slots, ctx->opt_slices);
 		lp->s_remote = 0;
 		const int key = (int)(sv.threads * sv.ipt);
 		if (ctx->sym_pairs_key != key) {
-			ctx->sym_pairs = sym_pair_evaluations((unsigned)ctx->n, lp->nb, lp->tpb);
+			ctx->sym_pairs = sym_pair_evaluations((unsigned)ctx->n, lp->nb, lp->tpb, lp->block0, lp->nb_own);
 			ctx->sym_pairs_key = key;
 		}
 		return NBODY_OK;
 	}
-	lp->nb = lp->tpb = lp->rows_pad = 0;
+	lp->nb = lp->tpb = lp->rows_pad = lp->block0 = lp->nb_own = 0;
 	lp->apart_stride = ctx->own_pad;
 	const Variant& v = variant_of(ctx);
 	const unsigned itile = v.threads * v.ipt;
@@ -456,6 +469,8 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.aj = ctx->aj;
 	p.rows_pad = lp.rows_pad;
 	p.nb = lp.nb;
+	p.block0 = lp.block0;
+	p.nb_own = lp.nb_own;
 	p.jt_total = lp.jt_total;
 	p.n_pad = ctx->n_pad;
 	p.n_real = (unsigned)ctx->n;
@@ -464,7 +479,7 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
 	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
 	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
-	const unsigned long long units = (unsigned long long)lp.nb * lp.s_local;
+	const unsigned long long units = (unsigned long long)lp.nb_own * lp.s_local;
 	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
 	if (ctx->opt_time_kernels) {
@@ -484,6 +499,18 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	if (e1) CK(cudaEventRecord(e1, ctx->sc));
 	ctx->tm.force_launches++;
 	ctx->tm.total_launches++;
+	if (ctx->world > 1) {
+		// every rank has collected reactions for ALL bodies its walk touched: sum them over the
+		// ranks, each rank keeping the rows it owns (in place: rows_pad == world * own_pad here)
+		const int dt = ctx->prec == 64 ? NCCL_DOUBLE : NCCL_FLOAT;
+		CKN(g_nccl.GroupStart());
+		for (int c = 0; c < 3; ++c) {
+			char* base = (char*)ctx->aj + (size_t)c * lp.rows_pad * ctx->esz;
+			CKN(g_nccl.ReduceScatter(base, base + (size_t)ctx->rank * ctx->own_pad * ctx->esz,
+									 ctx->own_pad, dt, NCCL_SUM, ctx->comm, ctx->sc));
+		}
+		CKN(g_nccl.GroupEnd());
+	}
 	return NBODY_OK;
 }
 
@@ -530,6 +557,19 @@ int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, GatherMod
 	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
 	if (lp.sym) {
 		ctx->tm.pair_evaluations += ctx->sym_pairs;
+		if (ctx->world > 1) {
+			// the walk of a block reaches half-way round the ring of blocks, so the whole stage
+			// array must be present: wait for the exchange (tens of microseconds against a launch
+			// of tens of milliseconds) instead of splitting the launch into local and remote tiles
+			int rc;
+			if (mode == GATHER_NOW) {
+				if ((rc = enqueue_gather(ctx, buf_ptr(ctx, buf), ctx->e_g))) return rc;
+				CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
+			} else if (mode == GATHER_PENDING_Y) {
+				CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
+				ctx->y_pending = false;
+			}
+		}
 		return launch_force_sym_all(ctx, lp, buf);
 	}
 	ctx->tm.pair_evaluations += (uint64_t)ctx->own_real * (uint64_t)ctx->n;
@@ -910,11 +950,7 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "variant out of range");
 		ctx->opt_variant = value;
 	} else if (k == "use_graph") ctx->opt_use_graph = value;
-	else if (k == "pair_symmetry") {
-		if (value != 0 && ctx->world > 1)
-			return fail(ctx, NBODY_ERR_STATE, "option \"pair_symmetry\" needs a single-GPU context");
-		ctx->opt_pair_symmetry = value != 0;
-	} else if (k == "sym_variant") {
+	else if (k == "pair_symmetry") ctx->opt_pair_symmetry = value != 0; else if (k == "sym_variant") {
 		const int nv = ctx->prec == 64 ? N_SYM64 : N_SYM32;
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "sym_variant out of range");
 		ctx->opt_sym_variant = value;

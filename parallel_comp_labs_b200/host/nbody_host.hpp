@@ -346,6 +346,7 @@ struct RunOptions {
 	long out_every = 1;
 	long max_steps = 0;
 	long variant = -1;
+	bool pair_symmetry = false;	 // opt-in: evaluate each pair once (one GPU), see include/nbody_b200.h
 	bool report = false;
 };
 
@@ -411,6 +412,7 @@ class Solver_N_body {
 		};
 		if (nbody_set_params(ctx, (double)sys.G, (double)sys.eps)) return fail("set_params");
 		if (opt.variant >= 0 && nbody_set_option(ctx, "variant", opt.variant)) return fail("variant");
+		if (opt.pair_symmetry && nbody_set_option(ctx, "pair_symmetry", 1)) return fail("pair_symmetry");
 		if (nbody_upload_aos(ctx, sys.traj_init.data())) return fail("upload");
 
 		std::ofstream traj;

@@ -44,7 +44,7 @@ void usage() {
 		"           [--t-final 20|1] [--eps 1e-6] [--G 6.67e-11] [--precision 64|32]\n"
 		"           [--scheme rk2|rk4] [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
-		"           [--output-folder ../output] [--variant -1] [--report]\n"
+		"           [--output-folder ../output] [--variant -1] [--pair-symmetry] [--report]\n"
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
 		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
 		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)");
@@ -82,6 +82,7 @@ int run(const Args& a) {
 	if (opt.out_every < 1) opt.out_every = 1;
 	opt.max_steps = (long)a.num("max-steps", 0);
 	opt.variant = (long)a.num("variant", -1);
+	opt.pair_symmetry = a.has("pair-symmetry");
 	opt.report = a.has("report");
 
 	Solver_N_body<T> solver;

@@ -21,7 +21,7 @@ from parallel_comp_labs_b200 import generators
 
 
 @pytest.fixture(scope="module")
-def emu():
+def emu_lib():
     out = os.path.join(tempfile.mkdtemp(prefix="kemu"), "libkemu.so")
     subprocess.run(["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-Wno-unknown-pragmas",
                     "-shared", "-fPIC", "-o", out,
@@ -29,6 +29,14 @@ def emu():
     L = C.CDLL(out)
     L.emu_rhs.argtypes = [C.c_uint, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int,
                           C.c_uint, C.c_int, C.c_uint, C.c_void_p, C.c_char_p, C.c_int]
+    L.emu_rhs_sym_ranks.argtypes = [C.c_uint, C.c_void_p, C.c_double, C.c_double, C.c_uint, C.c_uint,
+                                    C.c_int, C.c_void_p, C.c_char_p, C.c_int]
+    return L
+
+
+@pytest.fixture(scope="module")
+def emu(emu_lib):
+    L = emu_lib
 
     def run(bodies, prec=64, eps=1e-6, G=6.67e-11, sym=0, ipt=2, slices=1, unimass=1, grid=2):
         b = np.ascontiguousarray(bodies, dtype=np.float64)
@@ -89,3 +97,20 @@ def test_emulated_kernels_eps_extremes_and_fp32(emu, oracle, sym, ipt):
     want = oracle.rhs(u)[:, 4:7]
     got = emu(u, prec=32, sym=sym, ipt=ipt, unimass=0)
     assert rel_inf(got, want) < 1e-4               # north_star's FP32 tolerance
+
+
+def test_emulated_pair_symmetric_kernel_on_several_ranks(emu_lib, oracle):
+    """world > 1: every rank walks its own blocks of the global schedule (block0, nb_own) and
+    collects reactions for all bodies; summing the j-side arrays over the ranks (the
+    reduce-scatter) and reducing the owned rows in K2 gives the reference operator."""
+    L = emu_lib
+    for n, world, slices, um in ((1000, 2, 1, 0), (1500, 3, 2, 1), (1900, 2, 2, 1)):
+        b = generators.uniform_bodies(n, seed=n)
+        if um:
+            b[:, 0] = 2e7
+        acc = np.full((n, 3), np.nan)
+        err = C.create_string_buffer(256)
+        rc = L.emu_rhs_sym_ranks(n, b.ctypes.data, 6.67e-11, 1e-6, world, slices, um,
+                                 acc.ctypes.data, err, 256)
+        assert rc == 0, (rc, err.value.decode())
+        assert rel_inf(acc, oracle.rhs(b)[:, 4:7]) < 1e-14

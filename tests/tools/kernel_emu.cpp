@@ -104,6 +104,8 @@ int rhs_impl(unsigned n, const double* bodies, double G, double eps, int sym, in
 		p.pos = Y.data();
 		p.nb = (jt_total + tpb - 1) / tpb;
 		p.rows_pad = p.nb * block;
+		p.block0 = 0;
+		p.nb_own = p.nb;
 		p.jt_total = jt_total;
 		p.n_pad = n_pad;
 		p.n_real = n;
@@ -151,7 +153,92 @@ int rhs_impl(unsigned n, const double* bodies, double G, double eps, int sym, in
 	for (size_t k = 0; k < (size_t)3 * n; ++k) acc_out[k] = (double)rhs[k];
 	return 0;
 }
+
+// The pair-symmetric kernel on `world` ranks (FP64, I = 4): every rank packs the whole array,
+// walks its own blocks of the global schedule and collects reactions for all bodies; the j-side
+// arrays are then summed over the ranks (what ncclReduceScatter does) and every rank's K2 reduces
+// its owned rows.  Parameters as launch_force_sym_all / make_plan fill them for world > 1.
+int rhs_sym_ranks(unsigned n, const double* bodies, double G, double eps, unsigned world,
+				  unsigned n_slices, int unimass, double* acc_out) {
+	typedef double T;
+	typedef double4 vec4;
+	constexpr unsigned BLOCK = 512, TPB = 2;
+	const unsigned per = (n + world - 1) / world;
+	const unsigned own_pad = (per + TJ - 1) / TJ * TJ, n_pad = own_pad * world;
+	if (own_pad % BLOCK) return -20;
+	const unsigned jt_total = n_pad / TJ, nb = jt_total / TPB, nb_own = own_pad / BLOCK;
+	bool um = unimass != 0;
+	for (unsigned i = 1; um && i < n; ++i) um = bodies[7 * (size_t)i] == bodies[0];
+	const T mass = um ? bodies[0] : 0., pad_pos = um ? 1e150 : 0.;
+	std::vector<T> aj_sum((size_t)3 * n_pad, 0.);
+	std::vector<std::vector<vec4>> apart(world);
+	std::vector<vec4> Y((size_t)n_pad + EXTRA_TILES * TJ), P(Y.size());
+	for (unsigned r = 0; r < world; ++r) {
+		std::vector<vec4> vel(own_pad);
+		void *y = Y.data(), *pp = P.data(), *v = vel.data();
+		emu::launch(dim3((n_pad + 255) / 256), dim3(256), 0, [&] {
+			pack_aos_kernel<T>(bodies, y, pp, v, n, n_pad, r * own_pad, own_pad, pad_pos, um ? mass : 0.);
+		});
+		unsigned counter = 0;
+		std::vector<T> aj((size_t)3 * n_pad, 0.);
+		apart[r].assign((size_t)n_slices * own_pad, vec4{NAN, NAN, NAN, NAN});
+		SymParams p;
+		memset(&p, 0, sizeof(p));
+		p.pos = Y.data();
+		p.apart = apart[r].data();
+		p.aj = aj.data();
+		p.rows_pad = nb * BLOCK;
+		p.nb = nb;
+		p.block0 = r * nb_own;
+		p.nb_own = nb_own;
+		p.jt_total = jt_total;
+		p.n_pad = n_pad;
+		p.n_real = n;
+		p.n_slices = n_slices;
+		p.counter = &counter;
+		p.pad_pos = pad_pos;
+		const unsigned g = std::min(nb_own * n_slices, 2u);
+		um ? run_sym<T, 4, 1>(p, eps * eps, g) : run_sym<T, 4, 0>(p, eps * eps, g);
+		for (size_t k = 0; k < aj.size(); ++k) aj_sum[k] += aj[k];
+	}
+	for (unsigned r = 0; r < world; ++r) {
+		const unsigned own0 = r * own_pad;
+		const unsigned own_real = own0 >= n ? 0 : std::min(own_pad, n - own0);
+		if (!own_real) continue;
+		std::vector<T> rhs((size_t)3 * own_pad, NAN);
+		StageParams<T> sp;
+		memset((void*)&sp, 0, sizeof(sp));
+		sp.apart = apart[r].data();
+		sp.Y = Y.data();
+		sp.P = P.data();
+		sp.rhs_out = rhs.data();
+		sp.own0 = own0;
+		sp.own_pad = own_pad;
+		sp.own_real = own_real;
+		sp.n_slices = n_slices;
+		sp.apart_stride = nb_own * BLOCK;
+		sp.aj = aj_sum.data();
+		sp.aj_stride = nb * BLOCK;
+		sp.mass_scale = um ? mass : 1.;
+		sp.minusG = -G;
+		sp.first = 1;
+		emu::launch(dim3((own_real + 255) / 256), dim3(256), 0, [&] { stage_kernel<T>(sp); });
+		for (size_t k = 0; k < (size_t)3 * own_real; ++k) acc_out[3 * (size_t)own0 + k] = rhs[k];
+	}
+	return 0;
+}
 }  // namespace
+
+extern "C" int emu_rhs_sym_ranks(unsigned n, const double* bodies, double G, double eps,
+								 unsigned world, unsigned n_slices, int unimass, double* acc_out,
+								 char* err, int err_len) {
+	try {
+		return rhs_sym_ranks(n, bodies, G, eps, world, n_slices, unimass, acc_out);
+	} catch (const std::exception& e) {
+		if (err && err_len > 0) snprintf(err, (size_t)err_len, "%s", e.what());
+		return -1;
+	}
+}
 
 // bodies: n x {m,x,y,z,vx,vy,vz} doubles; acc_out: n x 3 doubles.  precision 64 | 32.
 // sym = 0: force_kernel<T,128,ipt,...> (ipt 2 | 4); sym = 1: force_sym_kernel (ipt 2|4|6|8).

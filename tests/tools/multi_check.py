@@ -21,6 +21,7 @@ def fresh_uid():  # one NCCL unique id per communicator (= per context)
     return box[0]
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 5000
 P2P = os.environ.get("NBODY_P2P", "0") == "1"
+PAIR_SYM = os.environ.get("NBODY_PAIR_SYM", "0") == "1"   # pair-symmetric kernel + reduce-scatter
 o = Oracle()
 ok = True
 for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1e-6, 0.1),
@@ -33,6 +34,8 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
                 dist.all_gather_object(blobs, ctx.p2p_export())
                 ctx.p2p_connect(blobs)
             ctx.set_params(6.67e-11, eps)
+            if PAIR_SYM:
+                ctx.set_option("pair_symmetry", 1)
             ctx.upload_aos(bodies)
             b, e = ctx.owned_range()
             a = ctx.rhs().astype(np.float64)
@@ -71,4 +74,5 @@ dist.destroy_process_group()
 if flag.item():
     print("MULTI-GPU CHECK FAILED"); sys.exit(1)
 if rank == 0:
-    print("MULTI-GPU CHECK PASSED" + (" (peer-pull exchange)" if P2P else " (NCCL all-gather)"))
+    print("MULTI-GPU CHECK PASSED" + (" (peer-pull exchange)" if P2P else " (NCCL all-gather)")
+          + (" (pair-symmetric kernel)" if PAIR_SYM else ""))
