@@ -109,7 +109,8 @@ int nbody_set_params(nbody_ctx* ctx, double G, double eps);
  * law) -- same per-pair bits, about half the arithmetic; j-side sums are collected with
  * floating-point atomics, so results are reproducible to rounding only; on several GPUs the
  * ranks split the blocks of one global schedule and the j-side sums are reduce-scattered
- * (needs the per-rank block of nbody_partition to be a multiple of 512 rows, NCCL exchange)),
+ * (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose block divides the
+ * per-rank block of nbody_partition, a forced variant that does not is NBODY_ERR_STATE)),
  * "sym_variant" (kernel variant id of that mode, -1 = default). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 

@@ -53,7 +53,12 @@ def lib() -> C.CDLL:
         raise NBodyError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
                          f"g.build()'` (or make -C parallel_comp_labs_b200/csrc). "
                          f"There is no CPU fallback.")
-    L = C.CDLL(LIB_PATH)
+    _lib = _bind(C.CDLL(LIB_PATH))
+    return _lib
+
+
+def _bind(L: C.CDLL) -> C.CDLL:
+    """Declare the C signatures of include/nbody_b200.h on a loaded library."""
     vp, sz = C.c_void_p, C.c_size_t
     L.nbody_version.restype = C.c_char_p
     L.nbody_last_error.restype = C.c_char_p
@@ -88,7 +93,6 @@ def lib() -> C.CDLL:
     L.nbody_host_free.argtypes = [vp]
     L.nbody_host_free.restype = None
     L.nbody_measure_fma_peak.argtypes = [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
-    _lib = L
     return L
 
 

@@ -6,7 +6,13 @@
 // path has no NCCL dependency and a host process that already carries an NCCL (torch)
 // shares it.  There is NO CPU path in this file: every entry point that computes
 // launches sm_100a kernels or fails.
+// Under NBODY_HOST_EMU (tests/tools/nbody_capi_emu.cpp, TEST INFRASTRUCTURE) this file is compiled
+// by g++ against a stand-in CUDA runtime and every NB_LAUNCH runs the kernel SOURCE on the CPU, so
+// that the host logic below is exercised by the CPU test suite.  The product build never defines it.
+#ifndef NBODY_HOST_EMU
 #include <cuda_runtime.h>
+#define NB_LAUNCH(kern, grid, block, smem, stream, ...) kern<<<grid, block, smem, stream>>>(__VA_ARGS__)
+#endif
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -92,7 +98,8 @@ template <> Clamp<float> make_clamp<float>(double eps2) {
 
 template <typename T, int TH, int I, int ST, int MB, int UM, int UN, int ORD>
 void launch_force(dim3 grid, cudaStream_t s, size_t smem, const ForceParams& p, double eps2) {
-	force_kernel<T, TH, I, ST, MB, UM, UN, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
+	auto kern = force_kernel<T, TH, I, ST, MB, UM, UN, ORD>;
+	NB_LAUNCH(kern, grid, dim3(TH), smem, s, p, make_clamp<T>(eps2));
 }
 #define NB_VARIANT(T, TH, I, ST, MB, UN, ORD)                                                  \
 	Variant { TH, I, force_smem_bytes<T, ST>(),                                                \
@@ -130,7 +137,8 @@ struct SymVariant {
 };
 template <typename T, int TH, int I, int ST, int MB, int UM, int ORD>
 void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p, double eps2) {
-	force_sym_kernel<T, TH, I, ST, MB, UM, ORD><<<grid, TH, smem, s>>>(p, make_clamp<T>(eps2));
+	auto kern = force_sym_kernel<T, TH, I, ST, MB, UM, ORD>;
+	NB_LAUNCH(kern, grid, dim3(TH), smem, s, p, make_clamp<T>(eps2));
 }
 #define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD)                                                  \
 	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
@@ -149,6 +157,7 @@ const SymVariant g_sym64[] = {
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2),
 	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2),
+	NB_SYM_VARIANT(float, 128, 2, 2, 8, 2),
 };
 constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
 constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);
@@ -253,8 +262,13 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
 	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
 	long v = c->opt_sym_variant;
-	if (v < 0 || v >= nv) v = 0;
-	return tab[v];
+	if (v >= 0 && v < nv) return tab[v];
+	// auto: the first variant whose block (threads * i-bodies) divides the per-rank block of the
+	// partition -- on several GPUs the ranks must own whole blocks; 256-row blocks always fit
+	if (c->world > 1)
+		for (int k = 0; k < nv; ++k)
+			if (c->own_pad % (unsigned)(tab[k].threads * tab[k].ipt) == 0) return tab[k];
+	return tab[0];
 }
 
 // j-slices per launch.  Units (i-tile, j-slice) are handed out dynamically, so the tail is
@@ -531,13 +545,15 @@ int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
 int p2p_publish(nbody_ctx* ctx, StageBuf buf) {
 	ctx->epoch++;
 	ctx->epoch_of[buf] = ctx->epoch;
-	p2p_signal_kernel<<<1, 32, 0, ctx->sc>>>(ctx->d_peer_flags, ctx->world, ctx->rank, ctx->epoch);
+	NB_LAUNCH(p2p_signal_kernel, dim3(1), dim3(32), 0, ctx->sc, ctx->d_peer_flags, ctx->world, ctx->rank,
+			  ctx->epoch);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
 }
 int p2p_wait(nbody_ctx* ctx, StageBuf buf) {
-	p2p_wait_kernel<<<1, 32, 0, ctx->sc>>>(ctx->d_flags, ctx->world, ctx->rank, ctx->epoch_of[buf]);
+	NB_LAUNCH(p2p_wait_kernel, dim3(1), dim3(32), 0, ctx->sc, ctx->d_flags, ctx->world, ctx->rank,
+			  ctx->epoch_of[buf]);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
@@ -621,7 +637,8 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	p.final_scale = (T)final_scale;
 	p.first = first;
 	p.last = last;
-	stage_kernel<T><<<(ctx->own_real + 255) / 256, 256, 0, ctx->sc>>>(p);
+	auto kern = stage_kernel<T>;
+	NB_LAUNCH(kern, dim3((ctx->own_real + 255) / 256), dim3(256), 0, ctx->sc, p);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
@@ -1015,12 +1032,10 @@ int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
 	detect_uniform_mass(ctx, bodies, 7);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		pack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>(
-			(const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+		NB_LAUNCH(pack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, (const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
 			ctx->own0, ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		pack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>(
-			(const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+		NB_LAUNCH(pack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, (const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
 			ctx->own0, ctx->own_pad, ctx->unimass ? 1e18f : 0.f,
 			ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
@@ -1049,12 +1064,10 @@ int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* 
 	detect_uniform_mass(ctx, m, 1);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		pack_soa_kernel<double><<<g, 256, 0, ctx->sc>>>(
-			(const double*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
+		NB_LAUNCH(pack_soa_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, (const double*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
 			ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		pack_soa_kernel<float><<<g, 256, 0, ctx->sc>>>(
-			(const float*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
+		NB_LAUNCH(pack_soa_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, (const float*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
 			ctx->own_pad, ctx->unimass ? 1e18f : 0.f, ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
@@ -1224,10 +1237,10 @@ int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
 	if ((rc = ensure_y_gathered(ctx))) return rc;
 	const unsigned g = ((unsigned)ctx->n + 255) / 256;
 	if (ctx->prec == 64)
-		snapshot_pack_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, (double*)ctx->snap_dev[slot],
+		NB_LAUNCH(snapshot_pack_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, (double*)ctx->snap_dev[slot],
 															 (unsigned)ctx->n);
 	else
-		snapshot_pack_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, (float*)ctx->snap_dev[slot],
+		NB_LAUNCH(snapshot_pack_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, (float*)ctx->snap_dev[slot],
 															(unsigned)ctx->n);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
@@ -1287,10 +1300,10 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
 	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes + 64));
 	const unsigned g = ((unsigned)ctx->n + 255) / 256;
 	if (ctx->prec == 64)
-		unpack_aos_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, vel, (double*)ctx->d_aos,
+		NB_LAUNCH(unpack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, vel, (double*)ctx->d_aos,
 														  (unsigned)ctx->n);
 	else
-		unpack_aos_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, vel, (float*)ctx->d_aos,
+		NB_LAUNCH(unpack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, vel, (float*)ctx->d_aos,
 														 (unsigned)ctx->n);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
@@ -1310,16 +1323,16 @@ int nbody_diagnostics(nbody_ctx* ctx, double out[9]) {
 		const unsigned g = (ctx->own_real + 255) / 256;
 		const unsigned gm = std::min(g, 4u * (unsigned)ctx->n_sm);
 		if (ctx->prec == 64) {
-			energy_kernel<double><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
+			NB_LAUNCH(energy_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, (unsigned)ctx->n,
 														  ctx->own0, ctx->own_real, ctx->eps,
 														  ctx->G, ctx->d_energy);
-			moments_kernel<double><<<gm, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, ctx->own0,
+			NB_LAUNCH(moments_kernel<double>, dim3(gm), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, ctx->own0,
 															ctx->own_real, ctx->d_energy + 2);
 		} else {
-			energy_kernel<float><<<g, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, (unsigned)ctx->n,
+			NB_LAUNCH(energy_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, (unsigned)ctx->n,
 														 ctx->own0, ctx->own_real, ctx->eps,
 														 ctx->G, ctx->d_energy);
-			moments_kernel<float><<<gm, 256, 0, ctx->sc>>>(ctx->Y, ctx->vel_n, ctx->own0,
+			NB_LAUNCH(moments_kernel<float>, dim3(gm), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, ctx->own0,
 														   ctx->own_real, ctx->d_energy + 2);
 		}
 		CK(cudaGetLastError());
@@ -1374,9 +1387,9 @@ int nbody_measure_fma_peak(int device, int precision, double ms_target, double* 
 	for (int pass = 0; pass < 8; ++pass) {
 		CK(cudaEventRecord(e0, 0));
 		if (precision == 64)
-			fma_peak_kernel<double><<<blocks, threads>>>((double*)d, 0.999999, 1e-9, iters);
+			NB_LAUNCH(fma_peak_kernel<double>, dim3(blocks), dim3(threads), 0, 0, (double*)d, 0.999999, 1e-9, iters);
 		else
-			fma_peak_kernel<float><<<blocks, threads>>>((float*)d, 0.9999f, 1e-5f, iters);
+			NB_LAUNCH(fma_peak_kernel<float>, dim3(blocks), dim3(threads), 0, 0, (float*)d, 0.9999f, 1e-5f, iters);
 		CK(cudaEventRecord(e1, 0));
 		CK(cudaEventSynchronize(e1));
 		CK(cudaGetLastError());

@@ -1,0 +1,261 @@
+"""The whole C ABI executed on the CPU (TEST INFRASTRUCTURE, not a product path).
+
+tests/tools/nbody_capi_emu.cpp is parallel_comp_labs_b200/csrc/nbody_capi.cu -- the unmodified
+source of libnbody_b200.so -- compiled by g++ against a stand-in CUDA runtime
+(tests/tools/cuda_rt_emu.h) with every kernel launch executed by the fiber emulation
+(tests/tools/cuda_emu.h).  The cases below are small versions of tests/test_gpu_parity.py and
+tests/test_zz_gpu_pair_symmetry.py: they drive the library's host logic (launch plans, buffer
+sizing, stage sequencing, CUDA-graph replay, snapshot ring, uniform-mass detection, option
+handling) and the kernels' source through the same ctypes binding the GPU tests use, and compare
+with the oracle and the golden fixtures.  What they cannot show is anything about the hardware
+(PTX semantics, concurrency, timing): the `-m gpu` suite remains the parity proof.
+
+The emulated library is loaded only here, by swapping capi's library handle for the duration of
+this module; the shipped library has no CPU path and nbody_create fails without an sm_100 device
+(tests/test_host_logic.py::test_no_cpu_fallback)."""
+import ctypes as C
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, rel_inf
+from parallel_comp_labs_b200 import capi, generators, lab
+
+
+@pytest.fixture(scope="module", autouse=True)
+def emulated_library():
+    out = os.path.join(tempfile.mkdtemp(prefix="capiemu"), "libnbody_emu.so")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-Wno-unknown-pragmas",
+                    "-shared", "-fPIC", "-o", out,
+                    os.path.join(ROOT, "tests", "tools", "nbody_capi_emu.cpp"), "-ldl", "-lpthread"],
+                   check=True)
+    # ranks as threads of this process: a stand-in NCCL over shared host memory
+    fake = os.path.join(os.path.dirname(out), "libfake_nccl.so")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-shared", "-fPIC", "-o", fake,
+                    os.path.join(ROOT, "tests", "tools", "fake_nccl.cpp"), "-lpthread"], check=True)
+    old_env = os.environ.get("NBODY_NCCL_LIB")
+    os.environ["NBODY_NCCL_LIB"] = fake
+    real = capi._lib
+    capi._lib = capi._bind(C.CDLL(out))
+    yield capi._lib
+    capi._lib = real
+    if old_env is None:
+        os.environ.pop("NBODY_NCCL_LIB", None)
+    else:
+        os.environ["NBODY_NCCL_LIB"] = old_env
+
+
+def run_rhs(bodies, prec=64, eps=1e-6, G=6.67e-11, **options):
+    with capi.Context(bodies.shape[0], prec) as ctx:
+        ctx.set_params(G, eps)
+        for k, v in options.items():
+            ctx.set_option(k, v)
+        ctx.upload_aos(bodies)
+        return ctx.rhs().astype(np.float64), ctx.timing()
+
+
+def run_steps(bodies, scheme, tau, steps, prec=64, eps=1e-6, **options):
+    with capi.Context(bodies.shape[0], prec) as ctx:
+        ctx.set_params(6.67e-11, eps)
+        for k, v in options.items():
+            ctx.set_option(k, v)
+        ctx.upload_aos(bodies)
+        ctx.step(scheme, tau, steps, sync=True)
+        return ctx.download_aos().astype(np.float64)
+
+
+def check_state(got, want, init, tol):
+    assert np.array_equal(got[:, 0], want[:, 0])
+    assert rel_inf(got[:, 1:4], want[:, 1:4]) < tol
+    assert rel_inf(got[:, 4:7], want[:, 4:7]) < tol
+    dv = want[:, 4:7] - init[:, 4:7]
+    floor = 50 * 2.2e-16 * np.abs(want[:, 4:7]).max() / np.abs(dv).max()
+    assert rel_inf(got[:, 4:7] - init[:, 4:7], dv) < max(tol, floor)
+
+
+SYM = [{"pair_symmetry": 0}, {"pair_symmetry": 1}]
+
+
+@pytest.mark.parametrize("opts", SYM)
+def test_emulated_abi_rhs_golden_and_ragged(oracle, golden, opts):
+    got, tm = run_rhs(golden["body4"], **opts)
+    assert rel_inf(got, golden["ref_rhs_body4"]) < 1e-12 and tm.uniform_mass == 1
+    got, tm = run_rhs(golden["rand512"], **opts)
+    assert rel_inf(got, golden["ref_rhs_rand512"]) < 1e-12 and tm.uniform_mass == 0
+    assert tm.interactions == 512 * 512 and tm.pair_symmetry == opts["pair_symmetry"]
+    plu = golden["plummer1000_in"]
+    got, _ = run_rhs(plu, eps=1e-3, **opts)
+    assert np.all(np.isfinite(got))
+    assert rel_inf(got, golden["ref_rhs_plummer1000_eps1e-3"]) < 1e-12
+    for n in (1, 3, 257, 777):
+        b = generators.uniform_bodies(n, seed=100 + n)
+        got, _ = run_rhs(b, **opts)
+        want = oracle.rhs(b)[:, 4:7]
+        assert (np.all(got == 0) if n == 1 else rel_inf(got, want) < 1e-12), n
+
+
+def test_emulated_abi_variants_slices_and_fp32(oracle):
+    b = generators.plummer_bodies(1300, seed=5)
+    b[7, 1:4] = b[8, 1:4] + 1e-5
+    b[900, 1:4] = b[20, 1:4]
+    want = oracle.rhs(b, eps=1e-3, threads=8)[:, 4:7]
+    for opts in ({"variant": 1}, {"variant": 5, "slices": 3}, {"slices": 5}, {"unimass": 0},
+                 {"pair_symmetry": 1, "sym_variant": 1, "slices": 2},
+                 {"pair_symmetry": 1, "sym_variant": 2}, {"pair_symmetry": 1, "sym_variant": 4},
+                 {"pair_symmetry": 1, "unimass": 0, "slices": 3}):
+        got, tm = run_rhs(b, eps=1e-3, **opts)
+        tol = 1e-11 if opts.get("variant") == 5 else 1e-12       # variant 5: first-order correction
+        assert np.all(np.isfinite(got)) and rel_inf(got, want) < tol, opts
+        if opts.get("pair_symmetry"):
+            assert 0.5 * 1300 * 1300 <= tm.pair_evaluations < 1300 * 1300, opts
+    mask = np.ones(1300, bool)
+    mask[[7, 8, 900, 20]] = False
+    for opts in ({}, {"pair_symmetry": 1}):
+        got, _ = run_rhs(b, prec=32, eps=1e-3, **opts)
+        assert np.abs(got[mask] - want[mask]).max() / np.abs(want[mask]).max() < 1e-4, opts
+
+
+@pytest.mark.parametrize("opts", SYM)
+def test_emulated_abi_rk2_rows_match_reference(golden, opts):
+    """The reference's own scheme on its own 4-body problem, first rows of the committed
+    trajectory (generated by the reference build), through the CUDA-graph replay path."""
+    b4 = golden["body4"]
+    rows = golden["ref_rk2_4body_0100"]          # [t, x1, y1, z1, ...] per step, t_start first
+    with capi.Context(4, 64) as ctx:
+        for k, v in opts.items():
+            ctx.set_option(k, v)
+        ctx.set_option("use_graph", 1)
+        ctx.upload_aos(b4)
+        for step in range(1, 6):
+            ctx.step(capi.NBODY_RK2, 0.1, 1, sync=True)
+            snap = ctx.snapshot()
+            assert rel_inf(snap.ravel(), rows[step, 1:]) < 1e-12, step
+
+
+@pytest.mark.parametrize("opts", SYM)
+def test_emulated_abi_rk4_and_tableau(oracle, golden, opts):
+    uni = generators.uniform_bodies(300, seed=0x5EED0001)
+    want, _ = oracle.rk4(uni, 0.1, 0.0, 1.0, max_steps=2, rows=False, threads=8)
+    for graph in (0, 1):
+        check_state(run_steps(uni, capi.NBODY_RK4, 0.1, 2, use_graph=graph, **opts), want, uni, 1e-10)
+    plu = golden["plummer1000_in"][:400].copy()
+    want, _ = oracle.rk4(plu, 1e-3, 0.0, 1.0, eps=1e-3, max_steps=2, rows=False, threads=8)
+    check_state(run_steps(plu, capi.NBODY_RK4, 1e-3, 2, eps=1e-3, use_graph=0, **opts), want, plu, 1e-10)
+    # Heun's third-order scheme through the tableau entry point
+    want = oracle.rk_subdiag(uni, [1 / 3, 2 / 3], [1, 0, 3], 0.25, 0.1, 0.0, 1.0, max_steps=2,
+                             threads=8)
+    with capi.Context(300, 64) as ctx:
+        for k, v in opts.items():
+            ctx.set_option(k, v)
+        ctx.upload_aos(uni)
+        ctx.step_tableau([1 / 3, 2 / 3], [1, 0, 3], 0.25, 0.1, 2, sync=True)
+        check_state(ctx.download_aos(), want, uni, 1e-10)
+
+
+def test_emulated_abi_mode_switch_soa_energy_and_errors(oracle, golden):
+    b = generators.uniform_bodies(600, seed=8)
+    with capi.Context(600, 64) as ctx:
+        ctx.upload_aos(b)
+        a0 = ctx.rhs()
+        ctx.set_option("pair_symmetry", 1)
+        a1 = ctx.rhs()
+        ctx.set_option("pair_symmetry", 0)
+        a2 = ctx.rhs()
+        assert np.array_equal(a0, a2) and rel_inf(a1, a0) < 1e-13
+        k, u = ctx.energy()
+        ko, uo = oracle.energy(b, threads=4)
+        assert abs(k - ko) <= 1e-12 * abs(ko) and abs(u - uo) <= 1e-10 * abs(uo)
+        with pytest.raises(capi.NBodyError):
+            ctx.set_option("sym_variant", 99)
+        with pytest.raises(capi.NBodyError):
+            ctx.set_option("no_such_option", 1)
+    # lab_5 SoA upload == AoS upload
+    r4 = np.zeros((600, 4)); r4[:, :3] = b[:, 1:4]
+    v4 = np.zeros((600, 4)); v4[:, :3] = b[:, 4:7]
+    with capi.Context(600, 64) as ctx:
+        ctx.set_option("pair_symmetry", 1)
+        ctx.upload_soa(b[:, 0], r4, v4)
+        assert rel_inf(ctx.rhs(), a1) < 1e-13
+        assert np.array_equal(ctx.download_aos(), b)
+
+
+def test_emulated_abi_python_host_mirror_writes_reference_rows(golden, tmp_path):
+    """lab.py's Solver over the emulated library: the lab_4-flavour trajectory file of the 4-body
+    test, header and first rows byte-compatible in layout, values within tolerance of the
+    reference build's rows."""
+    b4 = golden["body4"]
+    rows = golden["ref_rk2_4body_0100"]
+    got = []
+    with capi.Context(4, 64) as ctx:
+        ctx.upload_aos(b4)
+        got.append(ctx.snapshot().ravel())
+        for _ in range(10):
+            ctx.step(capi.NBODY_RK2, 0.1, 1, sync=True)
+            got.append(ctx.snapshot().ravel())
+    got = np.array(got)
+    assert rel_inf(got, rows[:11, 1:]) < 1e-12
+    line = lab.format_row(0.1, got[1].reshape(4, 3))
+    assert line.endswith(";\n") and line.count(";") == 13
+    assert line.startswith("1.0000000000000001e-01;9.9718778761114324e-01;9.0000000000000011e-02;")
+    # (the reference's own first row, reproduced here digit for digit)
+
+
+def _run_ranks(world, bodies, eps, tau, steps, **options):
+    """One emulated context per rank, ranks as threads (tests/tools/fake_nccl.cpp)."""
+    import threading
+    n = bodies.shape[0]
+    uid = capi.nccl_unique_id()
+    out, errs = [None] * world, []
+
+    def work(r):
+        try:
+            with capi.Context(n, 64, 0, r, world, uid) as ctx:
+                ctx.set_params(6.67e-11, eps)
+                for k, v in options.items():
+                    ctx.set_option(k, v)
+                ctx.upload_aos(bodies)
+                acc = ctx.rhs()
+                b, e = ctx.owned_range()
+                ctx.step(capi.NBODY_RK4, tau, steps)
+                snap = ctx.snapshot() if r == 0 else None       # not a collective
+                fin = ctx.download_aos()
+                out[r] = dict(acc=acc, rows=(b, e), fin=fin, snap=snap, diag=ctx.diagnostics())
+        except Exception as ex:                                  # noqa: BLE001
+            errs.append((r, repr(ex)))
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(600)
+    assert not errs and all(o is not None for o in out), errs
+    return out
+
+
+@pytest.mark.parametrize("world,opts", [(2, {}), (3, {}), (2, {"pair_symmetry": 1}),
+                                        (3, {"pair_symmetry": 1, "slices": 2})])
+def test_emulated_abi_several_ranks(oracle, world, opts):
+    """world > 1 through the whole ABI: block partition, all-gather of the stage positions (and the
+    eager gather of y_{n+1}), for the pair-symmetric kernel the reduce-scatter of the j-side sums,
+    gathered download, all-reduced diagnostics -- against the oracle, every rank."""
+    n = 1100
+    b = generators.plummer_bodies(n, seed=17)
+    want_a = oracle.rhs(b, eps=1e-3, threads=8)[:, 4:7]
+    want, _ = oracle.rk4(b, 1e-3, 0.0, 1.0, eps=1e-3, max_steps=2, rows=False, threads=8)
+    ko, uo = oracle.energy(want, eps=1e-3, threads=8)
+    res = _run_ranks(world, b, 1e-3, 1e-3, 2, **opts)
+    covered = np.zeros(n, bool)
+    for r, o in enumerate(res):
+        lo, hi = o["rows"]
+        covered[lo:hi] = True
+        assert np.all(np.isnan(o["acc"][:lo])) and np.all(np.isnan(o["acc"][hi:]))
+        if hi > lo:
+            assert np.abs(o["acc"][lo:hi] - want_a[lo:hi]).max() / np.abs(want_a).max() < 1e-12
+        check_state(o["fin"], want, b, 1e-10)
+        assert np.array_equal(o["fin"], res[0]["fin"])           # every rank downloads the same state
+        d = o["diag"]
+        assert abs(d["kinetic"] + d["potential"] - (ko + uo)) < 1e-9 * abs(ko + uo)
+    assert covered.all()
+    assert np.array_equal(res[0]["snap"], res[0]["fin"][:, 1:4])

@@ -35,7 +35,7 @@
 #define __forceinline__ inline
 #define __launch_bounds__(...)
 #define __align__(n) alignas(n)
-#define __shared__ static
+#define __shared__ static thread_local
 
 struct double4 { double x, y, z, w; };
 struct float4 { float x, y, z, w; };
@@ -68,10 +68,11 @@ struct Cta {
 	std::map<const void*, std::vector<long long>> waited;
 };
 
-inline Cta*& cta() { static Cta* c = nullptr; return c; }
-inline Fiber*& cur() { static Fiber* f = nullptr; return f; }
-inline ucontext_t& sched_ctx() { static ucontext_t c; return c; }
-inline std::string& failure() { static std::string s; return s; }
+// all emulation state is per OS thread: rank threads of one process may emulate concurrently
+inline Cta*& cta() { static thread_local Cta* c = nullptr; return c; }
+inline Fiber*& cur() { static thread_local Fiber* f = nullptr; return f; }
+inline ucontext_t& sched_ctx() { static thread_local ucontext_t c; return c; }
+inline std::string& failure() { static thread_local std::string s; return s; }
 
 inline void yield() { swapcontext(&cur()->ctx, &sched_ctx()); }
 
@@ -119,7 +120,7 @@ inline uint64_t warp_slot(unsigned par, unsigned lane) {
 }
 
 struct Entry { std::function<void()> fn; };
-inline Entry*& entry() { static Entry* e = nullptr; return e; }
+inline Entry*& entry() { static thread_local Entry* e = nullptr; return e; }
 inline void trampoline() {
 	entry()->fn();
 	cur()->done = true;
