@@ -147,6 +147,25 @@ int nbody_sync(nbody_ctx* ctx);
 int nbody_step_tableau(nbody_ctx* ctx, int n_stages, const double* a_sub /* n_stages-1 */,
 					   const double* b /* n_stages */, double scale, double tau, long n_steps);
 
+/* General explicit Runge-Kutta schemes, the whole Butcher tableau as data (SURVEY.md 8f row 4:
+ * "adaptive/other tableaux (RK3/RK45)"; not in the reference, whose only scheme is the midpoint
+ * rule of ode_RK2_MPI.hpp:72-92).  All stage derivatives of the owned rows stay resident;
+ *   k_s = f(y + tau sum_{j<s} a[s][j] k_j),   y += tau sum_s b[s] k_s.
+ * a: n_stages x n_stages, row-major, only the strictly lower triangle is read; b: n_stages.
+ * Same RHS kernels and exchange as nbody_step; one fused stage kernel per stage. */
+int nbody_step_rk(nbody_ctx* ctx, int n_stages, const double* a, const double* b, double tau,
+				  long n_steps);
+
+/* ONE step of an embedded pair (b: weights of the solution that is propagated, b_err: weights of
+ * the companion): additionally returns, synchronously, the max-norms over all bodies and
+ * components  norms = {|err_r|, |err_v|, |r_new|, |v_new|},  err = tau sum_s (b[s]-b_err[s]) k_s,
+ * and keeps the state the step started from so that a step-size controller on the host can
+ * reject it with nbody_step_undo (valid until the next call that changes the state).
+ * Collective when world > 1 (an all-reduce of the norms); NCCL exchange only. */
+int nbody_step_embedded(nbody_ctx* ctx, int n_stages, const double* a, const double* b,
+						const double* b_err, double tau, double norms[4]);
+int nbody_step_undo(nbody_ctx* ctx);
+
 /* Asynchronous position snapshot (replaces the per-step cudaMemcpyAsync D2H +
  * write_bodies_coords of lab_5 N_body.cu:352-367 and rank 0's row write of lab_4
  * ode_RK2_MPI.hpp:94-96).  Enqueues a device-side pack of all n positions (3 x T per

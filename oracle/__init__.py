@@ -58,6 +58,9 @@ class Oracle:
         L.oracle_rk_subdiag_f64.argtypes = [_dp, C.c_size_t, C.c_int, _dp, _dp, C.c_double,
                                             C.c_double, C.c_double, C.c_double, C.c_double,
                                             C.c_double, C.c_long, C.c_int]
+        L.oracle_rk_general_f64.restype = C.c_long
+        L.oracle_rk_general_f64.argtypes = [_dp, C.c_size_t, C.c_int, _dp, _dp, _dp, C.c_double,
+                                            C.c_long, C.c_double, C.c_double, C.c_int, _dp]
         L.oracle_rk2_f32.restype = C.c_long
         L.oracle_rk2_f32.argtypes = [_fp, C.c_size_t, C.c_float, C.c_float, C.c_float,
                                      C.c_float, C.c_float, _fp, C.c_long, C.c_long, C.c_int]
@@ -133,6 +136,22 @@ class Oracle:
                                      a.ctypes.data_as(_dp), b.ctypes.data_as(_dp), scale, tau,
                                      t_start, t_final, eps, G, max_steps, threads)
         return x
+
+    def rk_general(self, bodies, a, b, tau, n_steps, b_err=None, eps=1e-6, G=6.67e-11, threads=1):
+        """General explicit RK with the whole tableau as data (not in the reference): returns
+        (final state, err[4] of the last step = max|err_r|, max|err_v|, max|r|, max|v|)."""
+        x = _aos(bodies, np.float64).copy()
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        s = b.size
+        assert a.shape == (s, s)
+        be = None if b_err is None else np.ascontiguousarray(b_err, dtype=np.float64)
+        err = np.zeros(4)
+        self.L.oracle_rk_general_f64(x.ctypes.data_as(_dp), x.shape[0], s, a.ctypes.data_as(_dp),
+                                     b.ctypes.data_as(_dp),
+                                     be.ctypes.data_as(_dp) if be is not None else None,
+                                     tau, n_steps, eps, G, threads, err.ctypes.data_as(_dp))
+        return x, err
 
     def rk2_f32(self, bodies, tau, t_start, t_final, eps=1e-6, G=6.67e-11, max_steps=0,
                 rows=True, threads=1):

@@ -338,6 +338,70 @@ long oracle_rk_subdiag_f64(body_f64* sol, size_t n, int n_stages, const double* 
 	return steps;
 }
 
+/* General explicit Runge-Kutta step(s) with the whole tableau as data:
+ *   k_s = f(y + tau sum_{j<s} a[s][j] k_j),  y_new = y + tau sum_s b[s] k_s,
+ *   err = tau sum_s (b[s] - b_err[s]) k_s   (embedded pair; b_err may be NULL).
+ * NOT IN THE REFERENCE ("adaptive/other tableaux (RK3/RK45)"); the RHS is
+ * the reference operator above.  a is n_stages x n_stages row-major, strictly lower triangle
+ * read.  Rounding sequence: every coefficient is first multiplied by tau (tau*a, tau*b,
+ * tau*(b-b_err)), stage combinations are accumulated left to right as x = x + (c_j * k_j), zero
+ * coefficients skipped.  err_out[4] (last step) = {max|err_r|, max|err_v|, max|r_new|, max|v_new|}. */
+long oracle_rk_general_f64(body_f64* sol, size_t n, int n_stages, const double* a, const double* b,
+						   const double* b_err, double tau, long n_steps, double eps, double G,
+						   int n_threads, double* err_out) {
+	body_f64** k = (body_f64**)calloc((size_t)n_stages, sizeof(body_f64*));
+	for (int s = 0; s < n_stages; ++s) k[s] = (body_f64*)calloc(n, sizeof(body_f64));
+	body_f64* tmp = (body_f64*)calloc(n, sizeof(body_f64));
+	long steps = 0;
+	for (; steps < n_steps; ++steps) {
+		for (int s = 0; s < n_stages; ++s) {
+			for (size_t i = 0; i < n; ++i) {
+				tmp[i] = sol[i];
+				for (int j = 0; j < s; ++j) {
+					const double c = tau * a[s * n_stages + j];
+					if (c == 0.0) continue;
+					for (int d = 0; d < 3; ++d) {
+						tmp[i].r[d] = tmp[i].r[d] + c * k[j][i].r[d];
+						tmp[i].v[d] = tmp[i].v[d] + c * k[j][i].v[d];
+					}
+				}
+			}
+			oracle_rhs_f64(tmp, k[s], n, 0, n, eps, G, n_threads);
+		}
+		double e[4] = {0, 0, 0, 0};
+		for (size_t i = 0; i < n; ++i) {
+			double er[3] = {0, 0, 0}, ev[3] = {0, 0, 0};
+			for (int j = 0; j < n_stages; ++j) {
+				const double c = tau * b[j];
+				if (c != 0.0)
+					for (int d = 0; d < 3; ++d) {
+						sol[i].r[d] = sol[i].r[d] + c * k[j][i].r[d];
+						sol[i].v[d] = sol[i].v[d] + c * k[j][i].v[d];
+					}
+				if (b_err) {
+					const double ce = tau * (b[j] - b_err[j]);
+					if (ce != 0.0)
+						for (int d = 0; d < 3; ++d) {
+							er[d] = er[d] + ce * k[j][i].r[d];
+							ev[d] = ev[d] + ce * k[j][i].v[d];
+						}
+				}
+			}
+			for (int d = 0; d < 3; ++d) {
+				if (fabs(er[d]) > e[0]) e[0] = fabs(er[d]);
+				if (fabs(ev[d]) > e[1]) e[1] = fabs(ev[d]);
+				if (fabs(sol[i].r[d]) > e[2]) e[2] = fabs(sol[i].r[d]);
+				if (fabs(sol[i].v[d]) > e[3]) e[3] = fabs(sol[i].v[d]);
+			}
+		}
+		if (err_out) memcpy(err_out, e, sizeof(e));
+	}
+	for (int s = 0; s < n_stages; ++s) free(k[s]);
+	free(k);
+	free(tmp);
+	return steps;
+}
+
 /* FP32 explicit midpoint following the GPU flavour's update form.
  * lab_5_N_body_CUDA/src/N_body.cu:299-316 with mult_n_add (:120-127):
  *   k = f(r,v); r_tmp = r + (tau/2)*k_r; v_tmp = v + (tau/2)*k_v;

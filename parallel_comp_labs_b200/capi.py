@@ -80,6 +80,11 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_step.argtypes = [vp, C.c_int, C.c_double, C.c_long]
     L.nbody_step_tableau.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                      C.c_double, C.c_double, C.c_long]
+    L.nbody_step_rk.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                C.c_double, C.c_long]
+    L.nbody_step_embedded.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                      C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double)]
+    L.nbody_step_undo.argtypes = [vp]
     L.nbody_sync.argtypes = [vp]
     L.nbody_snapshot_async.argtypes = [vp, C.POINTER(C.c_uint64)]
     L.nbody_snapshot_wait.argtypes = [vp, C.c_uint64, C.POINTER(vp)]
@@ -236,6 +241,36 @@ class Context:
         self._ck(self.L.nbody_step_tableau(self.h, len(b), a, bb, scale, tau, n_steps))
         if sync:
             self.sync()
+
+    @staticmethod
+    def _tableau(a, b, b_err=None):
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        assert a.shape == (b.size, b.size), (a.shape, b.size)
+        dp = C.POINTER(C.c_double)
+        be = None if b_err is None else np.ascontiguousarray(b_err, dtype=np.float64)
+        assert be is None or be.shape == b.shape
+        return a, b, be, dp
+
+    def step_rk(self, a, b, tau: float, n_steps: int = 1, sync: bool = False):
+        """General explicit RK, whole tableau as data: a (s, s) strictly lower, b (s,)."""
+        a, b, _, dp = self._tableau(a, b)
+        self._ck(self.L.nbody_step_rk(self.h, b.size, a.ctypes.data_as(dp), b.ctypes.data_as(dp),
+                                      tau, n_steps))
+        if sync:
+            self.sync()
+
+    def step_embedded(self, a, b, b_err, tau: float) -> np.ndarray:
+        """One step of an embedded pair; returns [max|err_r|, max|err_v|, max|r|, max|v|]."""
+        a, b, be, dp = self._tableau(a, b, b_err)
+        out = np.zeros(4)
+        self._ck(self.L.nbody_step_embedded(self.h, b.size, a.ctypes.data_as(dp),
+                                            b.ctypes.data_as(dp), be.ctypes.data_as(dp), tau,
+                                            out.ctypes.data_as(dp)))
+        return out
+
+    def step_undo(self):
+        self._ck(self.L.nbody_step_undo(self.h))
 
     def sync(self):
         self._ck(self.L.nbody_sync(self.h))

@@ -36,7 +36,7 @@ namespace {
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0 };
+enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2 };
 struct NcclApi {
 	void* lib = nullptr;
 	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
@@ -182,6 +182,13 @@ struct nbody_ctx {
 	void* aj = nullptr;		 // T[3][aj_rows] j-side sums of the pair-symmetric kernel
 	unsigned aj_rows = 0;
 	long opt_pair_symmetry = 0, opt_sym_variant = -1;
+	// general tableaux (nbody_step_rk / nbody_step_embedded): resident stage derivatives, the
+	// norms of the last embedded step, and the state before it (nbody_step_undo)
+	void *kr = nullptr, *kv = nullptr;
+	int k_stages = 0;
+	double* d_norms = nullptr;
+	void *undo_Y = nullptr, *undo_vel = nullptr;
+	bool undo_valid = false;
 	uint64_t sym_pairs = 0;	 // pair evaluations of one symmetric RHS (cached with its key)
 	int sym_pairs_key = -1;
 	double* d_energy = nullptr;
@@ -644,6 +651,59 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	return NBODY_OK;
 }
 
+// Coefficients of one step of a general explicit RK scheme, already multiplied by tau in T.
+struct GenCoef {
+	int ns = 0;
+	bool want_err = false;
+	double a[NBODY_MAX_STAGES][NBODY_MAX_STAGES] = {};	// tau * a[s][j], j < s
+	double w[NBODY_MAX_STAGES] = {};					// tau * b[j]
+	double e[NBODY_MAX_STAGES] = {};					// tau * (b[j] - b_err[j])
+};
+
+template <typename T>
+int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, const GenCoef& k,
+						 int s) {
+	if (ctx->own_real == 0) return NBODY_OK;
+	StageGenParams<T> g;
+	StageParams<T>& p = g.base;
+	p.apart = ctx->apart;
+	p.Y = ctx->Y;
+	p.P = next_buf;
+	p.vel_n = ctx->vel_n;
+	p.vel_s = ctx->vel_s;
+	p.acc_r = ctx->acc_r;
+	p.acc_v = ctx->acc_v;
+	p.rhs_out = nullptr;
+	p.own0 = ctx->own0;
+	p.own_pad = ctx->own_pad;
+	p.own_real = ctx->own_real;
+	p.n_slices = lp.s_local + lp.s_remote;
+	p.apart_stride = lp.apart_stride;
+	p.aj = lp.sym ? ctx->aj : nullptr;
+	p.aj_stride = lp.rows_pad;
+	p.mass_scale = ctx->unimass ? (T)ctx->uniform_mass : T(1);
+	p.minusG = (T)(-(T)ctx->G);
+	p.c_next = p.b = p.final_scale = T(0);
+	p.first = s == 0;
+	p.last = s == k.ns - 1;
+	g.kr = ctx->kr;
+	g.kv = ctx->kv;
+	g.s = s;
+	g.n_stages = k.ns;
+	g.last = s == k.ns - 1;
+	g.want_err = g.last && k.want_err;
+	g.norms = g.want_err ? ctx->d_norms : nullptr;
+	for (int j = 0; j < NBODY_MAX_STAGES; ++j) {
+		g.c[j] = j <= s ? (T)(g.last ? k.w[j] : k.a[s + 1][j]) : T(0);
+		g.e[j] = (g.want_err && j <= s) ? (T)k.e[j] : T(0);
+	}
+	auto kern = stage_general_kernel<T>;
+	NB_LAUNCH(kern, dim3((ctx->own_real + 255) / 256), dim3(256), 0, ctx->sc, g);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	return NBODY_OK;
+}
+
 int stage_dispatch(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next_buf,
 				   double c_next, double b, double final_scale, int first, int last) {
 	return ctx->prec == 64
@@ -696,6 +756,29 @@ int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, const StepCoef& k) {
 		// Eager gather of y_{n+1}: every rank enqueues it here, so Y is whole on all ranks after
 		// every step without any later collective (snapshots, downloads and the energy of ONE
 		// rank only wait for e_gy); the next step's local-tile launch still overlaps it.
+		if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;
+		ctx->y_pending = true;
+	}
+	return NBODY_OK;
+}
+
+// one step of a general explicit RK scheme (all k_j resident), enqueued on sc (+ sm)
+int enqueue_step_general(nbody_ctx* ctx, const LaunchPlan& lp, const GenCoef& k) {
+	int rc;
+	for (int s = 0; s < k.ns; ++s) {
+		const StageBuf buf = stage_buf(ctx, s);
+		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
+		if ((rc = enqueue_forces(ctx, lp, buf, mode))) return rc;
+		const bool last = s == k.ns - 1;
+		const StageBuf nxt = last ? BUF_Y : stage_buf(ctx, s + 1);
+		rc = ctx->prec == 64 ? launch_stage_general<double>(ctx, lp, buf_ptr(ctx, nxt), k, s)
+							 : launch_stage_general<float>(ctx, lp, buf_ptr(ctx, nxt), k, s);
+		if (rc) return rc;
+		if (ctx->p2p && (rc = p2p_publish(ctx, nxt))) return rc;
+	}
+	if (ctx->p2p) {
+		ctx->y_stale = true;
+	} else if (ctx->world > 1) {
 		if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;
 		ctx->y_pending = true;
 	}
@@ -760,6 +843,7 @@ void nbody_destroy(nbody_ctx* ctx) {
 	if (ctx->comm && g_nccl.lib) g_nccl.CommDestroy(ctx->comm);
 	void* bufs[] = {ctx->Y, ctx->P, ctx->vel_n, ctx->vel_s, ctx->acc_r, ctx->acc_v, ctx->apart,
 					ctx->rhs_out, ctx->vel_all, ctx->d_aos, ctx->d_energy, ctx->d_counters, ctx->aj,
+					ctx->kr, ctx->kv, ctx->d_norms, ctx->undo_Y, ctx->undo_vel,
 					ctx->P2, ctx->d_flags, ctx->d_peer_flags};
 	for (void* b : bufs)
 		if (b) cudaFree(b);
@@ -1009,6 +1093,7 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 }
 
 static int upload_common(nbody_ctx* ctx) {
+	ctx->undo_valid = false;
 	if (ctx->P2)  // pad rows and masses of the second stage buffer
 		CK(cudaMemcpy(ctx->P2, ctx->P, (size_t)ctx->n_pad * 4 * ctx->esz, cudaMemcpyDeviceToDevice));
 	if (ctx->p2p) {	 // peers read this rank's block of Y from here on: publish it
@@ -1112,6 +1197,7 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 }
 
 static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double tau, long n_steps) {
+	ctx->undo_valid = false;
 	if (n_steps < 0) return fail(ctx, NBODY_ERR_ARG, "n_steps < 0");
 	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step before upload");
 	CK(cudaSetDevice(ctx->device));
@@ -1179,6 +1265,116 @@ int nbody_step_tableau(nbody_ctx* ctx, int n_stages, const double* a_sub, const 
 	}
 	for (int s = 0; s < n_stages; ++s) k.b[s] = b[s];
 	return step_impl(ctx, k, /*graph_key: tableaux are not cached*/ 0, tau, n_steps);
+}
+
+// ---- general tableaux ------------------------------------------------------------------------
+static int make_gen_coef(nbody_ctx* ctx, int n_stages, const double* a, const double* b,
+						 const double* b_err, double tau, GenCoef* k) {
+	if (!a && n_stages > 1) return fail(ctx, NBODY_ERR_ARG, "null tableau");
+	if (!b) return fail(ctx, NBODY_ERR_ARG, "null weights");
+	if (n_stages < 1 || n_stages > NBODY_MAX_STAGES)
+		return fail(ctx, NBODY_ERR_ARG, "n_stages out of range");
+	k->ns = n_stages;
+	k->want_err = b_err != nullptr;
+	const bool f64 = ctx->prec == 64;
+	auto mul = [&](double x, double y) { return f64 ? x * y : (double)((float)x * (float)y); };
+	for (int s = 0; s < n_stages; ++s) {
+		for (int j = 0; j < s; ++j) k->a[s][j] = mul(tau, a[s * n_stages + j]);
+		k->w[s] = mul(tau, b[s]);
+		k->e[s] = b_err ? mul(tau, f64 ? b[s] - b_err[s] : (double)((float)b[s] - (float)b_err[s])) : 0.;
+	}
+	return NBODY_OK;
+}
+
+static int ensure_stage_store(nbody_ctx* ctx, int n_stages) {
+	if (n_stages <= ctx->k_stages) return NBODY_OK;
+	CK(cudaStreamSynchronize(ctx->sc));
+	if (ctx->kr) CK(cudaFree(ctx->kr));
+	if (ctx->kv) CK(cudaFree(ctx->kv));
+	ctx->kr = ctx->kv = nullptr;
+	ctx->k_stages = 0;
+	const size_t bytes = (size_t)n_stages * ctx->own_pad * 4 * ctx->esz;
+	CK(cudaMalloc(&ctx->kr, bytes));
+	CK(cudaMalloc(&ctx->kv, bytes));
+	ctx->k_stages = n_stages;
+	return NBODY_OK;
+}
+
+int nbody_step_rk(nbody_ctx* ctx, int n_stages, const double* a, const double* b, double tau,
+				  long n_steps) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	if (n_steps < 0) return fail(ctx, NBODY_ERR_ARG, "n_steps < 0");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step_rk before upload");
+	GenCoef k;
+	int rc;
+	if ((rc = make_gen_coef(ctx, n_stages, a, b, nullptr, tau, &k))) return rc;
+	CK(cudaSetDevice(ctx->device));
+	LaunchPlan lp;
+	if ((rc = make_plan(ctx, &lp))) return rc;
+	if ((rc = ensure_apart(ctx, lp))) return rc;
+	if ((rc = ensure_stage_store(ctx, n_stages))) return rc;
+	if ((rc = begin_timed_call(ctx))) return rc;
+	for (long done = 0; done < n_steps; ++done)
+		if ((rc = enqueue_step_general(ctx, lp, k))) return rc;
+	ctx->tm.steps_done += (uint64_t)n_steps;
+	ctx->undo_valid = false;
+	return end_timed_call(ctx);
+}
+
+int nbody_step_embedded(nbody_ctx* ctx, int n_stages, const double* a, const double* b,
+						const double* b_err, double tau, double norms[4]) {
+	if (!ctx || !b_err || !norms) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step_embedded before upload");
+	if (ctx->p2p)
+		return fail(ctx, NBODY_ERR_STATE, "nbody_step_embedded needs the NCCL exchange (undo copies Y)");
+	GenCoef k;
+	int rc;
+	if ((rc = make_gen_coef(ctx, n_stages, a, b, b_err, tau, &k))) return rc;
+	CK(cudaSetDevice(ctx->device));
+	LaunchPlan lp;
+	if ((rc = make_plan(ctx, &lp))) return rc;
+	if ((rc = ensure_apart(ctx, lp))) return rc;
+	if ((rc = ensure_stage_store(ctx, n_stages))) return rc;
+	const size_t v4 = 4 * ctx->esz;
+	if (!ctx->undo_Y) {
+		CK(cudaMalloc(&ctx->undo_Y, (size_t)ctx->n_pad * v4));
+		CK(cudaMalloc(&ctx->undo_vel, (size_t)ctx->own_pad * v4));
+	}
+	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 4 * sizeof(double)));
+	// the state this step starts from, whole (every rank holds all positions)
+	if ((rc = ensure_y_gathered(ctx))) return rc;
+	CK(cudaMemcpyAsync(ctx->undo_Y, ctx->Y, (size_t)ctx->n_pad * v4, cudaMemcpyDeviceToDevice, ctx->sc));
+	CK(cudaMemcpyAsync(ctx->undo_vel, ctx->vel_n, (size_t)ctx->own_pad * v4, cudaMemcpyDeviceToDevice,
+					   ctx->sc));
+	CK(cudaMemsetAsync(ctx->d_norms, 0, 4 * sizeof(double), ctx->sc));
+	if ((rc = begin_timed_call(ctx))) return rc;
+	if ((rc = enqueue_step_general(ctx, lp, k))) return rc;
+	if ((rc = end_timed_call(ctx))) return rc;
+	if (ctx->world > 1)
+		CKN(g_nccl.AllReduce(ctx->d_norms, ctx->d_norms, 4, NCCL_DOUBLE, NCCL_MAX, ctx->comm, ctx->sc));
+	CK(cudaMemcpyAsync(norms, ctx->d_norms, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	ctx->tm.steps_done += 1;
+	ctx->undo_valid = true;
+	return NBODY_OK;
+}
+
+int nbody_step_undo(nbody_ctx* ctx) {
+	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
+	if (!ctx->undo_valid)
+		return fail(ctx, NBODY_ERR_STATE, "nbody_step_undo: the last call was not nbody_step_embedded");
+	CK(cudaSetDevice(ctx->device));
+	const size_t v4 = 4 * ctx->esz;
+	if (ctx->y_pending) {  // the eager gather of the rejected y_{n+1} must land before Y is rewritten
+		CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
+		ctx->y_pending = false;
+	}
+	CK(cudaMemcpyAsync(ctx->Y, ctx->undo_Y, (size_t)ctx->n_pad * v4, cudaMemcpyDeviceToDevice, ctx->sc));
+	CK(cudaMemcpyAsync(ctx->vel_n, ctx->undo_vel, (size_t)ctx->own_pad * v4, cudaMemcpyDeviceToDevice,
+					   ctx->sc));
+	ctx->tm.steps_done -= 1;
+	ctx->undo_valid = false;
+	return NBODY_OK;
 }
 
 int nbody_sync(nbody_ctx* ctx) {

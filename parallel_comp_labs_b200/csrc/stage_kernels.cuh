@@ -126,6 +126,134 @@ __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
 	}
 }
 
+// ---------------------------------------------------------------- K2g: general tableau
+// The same fusion for ANY explicit Runge-Kutta tableau (not in the
+// reference): all stage derivatives k_j = (k_r, k_v) of the owned rows stay resident, stage s
+//   * reduces the partial sums to a_s (fixed order, * -G) and stores k_s = (v_stage, a_s),
+//   * forms the next stage state y_n + sum_{j<=s} c[j] k_j  (c[j] = tau * a[s+1][j]), or
+//   * on the last stage y_{n+1} = y_n + sum_j w[j] k_j  (w[j] = tau * b[j]) and, for an embedded
+//     pair, the error estimate sum_j e[j] k_j  (e[j] = tau * (b[j] - b_err[j])), whose max-norms
+//     go to `norms` = {max|err_r|, max|err_v|, max|r_new|, max|v_new|} (atomic max on the bit
+//     patterns of non-negative doubles).
+// Accumulation order: left to right, x = x + (c_j * k_j), zero coefficients skipped -- the
+// sequence of oracle_rk_general_f64.
+#define NBODY_MAX_STAGES_K2G 8
+template <typename T>
+struct StageGenParams {
+	StageParams<T> base;	// apart / aj / Y / P / vel_n / vel_s / own0 / own_pad / own_real / ...
+	void* kr;				// V4[n_stages][own_pad] stage derivatives, position part
+	void* kv;				// V4[n_stages][own_pad]                    velocity part
+	double* norms;			// [4] or null
+	int s, n_stages, last, want_err;
+	T c[NBODY_MAX_STAGES_K2G];	// next-stage coefficients (j <= s), or the weights w on the last stage
+	T e[NBODY_MAX_STAGES_K2G];	// error weights (last stage of an embedded pair)
+};
+
+__device__ __forceinline__ void atomic_max_nonneg(double* addr, double v) {
+	// v >= +0 or NaN: the bit patterns order like the values, NaN sorts above everything
+	atomicMax(reinterpret_cast<unsigned long long*>(addr),
+			  (unsigned long long)__double_as_longlong(v));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) stage_general_kernel(const StageGenParams<T> g) {
+	typedef typename V4<T>::type vec4;
+	const StageParams<T>& p = g.base;
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	const bool live = i < p.own_real;
+	double n_er = 0, n_ev = 0, n_r = 0, n_v = 0;
+	if (live) {
+		const vec4* apart = reinterpret_cast<const vec4*>(p.apart);
+		T ax = T(0), ay = T(0), az = T(0);
+		for (unsigned s = 0; s < p.n_slices; ++s) {
+			const vec4 q = apart[(size_t)s * p.apart_stride + i];
+			ax = add_rn(ax, q.x);
+			ay = add_rn(ay, q.y);
+			az = add_rn(az, q.z);
+		}
+		if (p.aj) {
+			const T* gj = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
+			ax = add_rn(ax, gj[0]);
+			ay = add_rn(ay, gj[(size_t)p.aj_stride]);
+			az = add_rn(az, gj[2 * (size_t)p.aj_stride]);
+		}
+		ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
+		ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
+		az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);
+
+		vec4* Y = reinterpret_cast<vec4*>(p.Y);
+		vec4* P = reinterpret_cast<vec4*>(p.P);
+		vec4* vel_n = reinterpret_cast<vec4*>(p.vel_n);
+		vec4* vel_s = reinterpret_cast<vec4*>(p.vel_s);
+		vec4* kr = reinterpret_cast<vec4*>(g.kr);
+		vec4* kv = reinterpret_cast<vec4*>(g.kv);
+		const vec4 yn = Y[(size_t)p.own0 + i];
+		const vec4 vn = vel_n[i];
+		vec4 ks_r = g.s == 0 ? vn : vel_s[i];  // k_s.r = stage velocity (diff.r = traj.v)
+		ks_r.w = T(0);
+		vec4 ks_v;
+		ks_v.x = ax; ks_v.y = ay; ks_v.z = az; ks_v.w = T(0);
+		if (!g.last) {	// later stages read it back; the last stage's k is used right here
+			kr[(size_t)g.s * p.own_pad + i] = ks_r;
+			kv[(size_t)g.s * p.own_pad + i] = ks_v;
+		}
+		T rx = yn.x, ry = yn.y, rz = yn.z, vx = vn.x, vy = vn.y, vz = vn.z;
+		T erx = T(0), ery = T(0), erz = T(0), evx = T(0), evy = T(0), evz = T(0);
+		for (int j = 0; j <= g.s; ++j) {
+			const T c = g.c[j];
+			const T e = g.want_err ? g.e[j] : T(0);
+			if (c == T(0) && e == T(0)) continue;
+			const vec4 a_r = j == g.s ? ks_r : kr[(size_t)j * p.own_pad + i];
+			const vec4 a_v = j == g.s ? ks_v : kv[(size_t)j * p.own_pad + i];
+			if (c != T(0)) {
+				rx = add_rn(rx, mul_rn(c, a_r.x)); ry = add_rn(ry, mul_rn(c, a_r.y)); rz = add_rn(rz, mul_rn(c, a_r.z));
+				vx = add_rn(vx, mul_rn(c, a_v.x)); vy = add_rn(vy, mul_rn(c, a_v.y)); vz = add_rn(vz, mul_rn(c, a_v.z));
+			}
+			if (e != T(0)) {
+				erx = add_rn(erx, mul_rn(e, a_r.x)); ery = add_rn(ery, mul_rn(e, a_r.y)); erz = add_rn(erz, mul_rn(e, a_r.z));
+				evx = add_rn(evx, mul_rn(e, a_v.x)); evy = add_rn(evy, mul_rn(e, a_v.y)); evz = add_rn(evz, mul_rn(e, a_v.z));
+			}
+		}
+		vec4 rn, vnew;
+		rn.x = rx; rn.y = ry; rn.z = rz; rn.w = yn.w;
+		vnew.x = vx; vnew.y = vy; vnew.z = vz; vnew.w = T(0);
+		if (!g.last) {
+			P[(size_t)p.own0 + i] = rn;
+			vel_s[i] = vnew;
+		} else {
+			Y[(size_t)p.own0 + i] = rn;
+			vel_n[i] = vnew;
+			if (g.norms) {
+				n_er = fmax(fmax(fabs((double)erx), fabs((double)ery)), fabs((double)erz));
+				n_ev = fmax(fmax(fabs((double)evx), fabs((double)evy)), fabs((double)evz));
+				n_r = fmax(fmax(fabs((double)rx), fabs((double)ry)), fabs((double)rz));
+				n_v = fmax(fmax(fabs((double)vx), fabs((double)vy)), fabs((double)vz));
+				// fmax drops NaN operands: keep them visible
+				if (erx != erx || ery != ery || erz != erz) n_er = (double)(erx + ery + erz);
+				if (evx != evx || evy != evy || evz != evz) n_ev = (double)(evx + evy + evz);
+			}
+		}
+	}
+	if (g.last && g.norms) {  // every thread of the block takes part in the shuffles
+		for (int o = 16; o > 0; o >>= 1) {
+			const double a = __shfl_down_sync(0xffffffffu, n_er, o);
+			const double b = __shfl_down_sync(0xffffffffu, n_ev, o);
+			const double c = __shfl_down_sync(0xffffffffu, n_r, o);
+			const double d = __shfl_down_sync(0xffffffffu, n_v, o);
+			n_er = (a > n_er || a != a) ? a : n_er;
+			n_ev = (b > n_ev || b != b) ? b : n_ev;
+			n_r = c > n_r ? c : n_r;
+			n_v = d > n_v ? d : n_v;
+		}
+		if ((threadIdx.x & 31) == 0) {
+			atomic_max_nonneg(g.norms + 0, n_er);
+			atomic_max_nonneg(g.norms + 1, n_ev);
+			atomic_max_nonneg(g.norms + 2, n_r);
+			atomic_max_nonneg(g.norms + 3, n_v);
+		}
+	}
+}
+
 // ---------------------------------------------------------------- layout kernels
 // AoS Body<T> (7 x T) -> packed {x,y,z,m} for all n bodies and {vx,vy,vz,0} for owned rows.
 template <typename T>

@@ -259,3 +259,103 @@ def test_emulated_abi_several_ranks(oracle, world, opts):
         assert abs(d["kinetic"] + d["potential"] - (ko + uo)) < 1e-9 * abs(ko + uo)
     assert covered.all()
     assert np.array_equal(res[0]["snap"], res[0]["fin"][:, 1:4])
+
+
+# ------------------------------------------------------------------ general tableaux (K2g)
+def test_emulated_abi_general_tableaux_vs_oracle(oracle):
+    from parallel_comp_labs_b200 import tableaux
+    plu = generators.plummer_bodies(160, seed=11)
+    for name, t in tableaux.TABLEAUX.items():
+        assert tableaux.check_order_conditions(name) < 1e-14, name
+        want, _ = oracle.rk_general(plu, t["a"], t["b"], 2e-3, 2, eps=1e-3, threads=8)
+        with capi.Context(160, 64) as ctx:
+            ctx.set_params(6.67e-11, 1e-3)
+            ctx.set_option("pair_symmetry", 1 if name in ("rk38", "dopri5") else 0)
+            ctx.upload_aos(plu)
+            ctx.step_rk(t["a"], t["b"], 2e-3, 2, sync=True)
+            check_state(ctx.download_aos(), want, plu, 1e-10)
+            assert ctx.timing().force_launches == 2 * len(t["b"])
+    # the tableau path and the hard-wired RK4 agree (different rounding sequence, same scheme)
+    t = tableaux.TABLEAUX["rk4"]
+    with capi.Context(160, 64) as ctx:
+        ctx.set_params(6.67e-11, 1e-3)
+        ctx.upload_aos(plu)
+        ctx.step(capi.NBODY_RK4, 2e-3, 2, sync=True)
+        hard = ctx.download_aos()
+        ctx.upload_aos(plu)
+        ctx.step_rk(t["a"], t["b"], 2e-3, 2, sync=True)
+        assert rel_inf(ctx.download_aos()[:, 1:7], hard[:, 1:7]) < 1e-13
+    # FP32
+    u32 = generators.uniform_bodies(200, seed=4)
+    t = tableaux.TABLEAUX["kutta3"]
+    want, _ = oracle.rk_general(u32, t["a"], t["b"], 0.1, 2, threads=8)
+    with capi.Context(200, 32) as ctx:
+        ctx.upload_aos(u32)
+        ctx.step_rk(t["a"], t["b"], 0.1, 2, sync=True)
+        got = ctx.download_aos().astype(np.float64)
+        assert rel_inf(got[:, 1:4], want[:, 1:4]) < 1e-4 and rel_inf(got[:, 4:7], want[:, 4:7]) < 1e-4
+
+
+def test_emulated_abi_embedded_step_undo_and_controller(oracle, golden):
+    from parallel_comp_labs_b200 import tableaux
+    plu = generators.plummer_bodies(160, seed=12)
+    for name in ("bs23", "rkf45", "cashkarp", "dopri5"):
+        t = tableaux.TABLEAUX[name]
+        want, werr = oracle.rk_general(plu, t["a"], t["b"], 5e-3, 1, b_err=t["b_err"], eps=1e-3,
+                                       threads=8)
+        with capi.Context(160, 64) as ctx:
+            ctx.set_params(6.67e-11, 1e-3)
+            ctx.upload_aos(plu)
+            norms = ctx.step_embedded(t["a"], t["b"], t["b_err"], 5e-3)
+            check_state(ctx.download_aos(), want, plu, 1e-10)
+            assert np.all(werr[:2] > 0), name
+            assert np.allclose(norms[:2], werr[:2], rtol=1e-4, atol=0), (name, norms, werr)
+            assert np.allclose(norms[2:], werr[2:], rtol=1e-12, atol=0)
+            ctx.step_undo()                                   # reject: back to the start, bit for bit
+            assert np.array_equal(ctx.download_aos(), plu)
+            with pytest.raises(capi.NBodyError):
+                ctx.step_undo()                               # nothing left to undo
+    # the reference's 4-body problem with step-size control, against the accurate fixture solution
+    b4 = golden["body4"]
+    with capi.Context(4, 64) as ctx:
+        ctx.upload_aos(b4)
+        info = tableaux.integrate_adaptive(ctx, "dopri5", 0.0, 2.0, 0.1, rtol=1e-10)
+        fin = ctx.download_aos()
+    assert abs(info["t"] - 2.0) < 1e-12 and info["accepted"] >= 5
+    assert np.abs(fin[0, 1:4] - golden["traj1"][20, 1:4]).max() < 2e-5      # fixture floor ~4e-6
+    fixed = 2.8e-3                                             # the reference's RK2 at tau = 0.025
+    assert np.abs(fin[0, 1:4] - golden["traj1"][20, 1:4]).max() < fixed
+
+
+def test_emulated_abi_embedded_step_on_two_ranks(oracle):
+    from parallel_comp_labs_b200 import tableaux
+    import threading
+    t = tableaux.TABLEAUX["bs23"]
+    b = generators.plummer_bodies(700, seed=13)
+    want, werr = oracle.rk_general(b, t["a"], t["b"], 5e-3, 1, b_err=t["b_err"], eps=1e-3, threads=8)
+    uid = capi.nccl_unique_id()
+    out, errs = [None, None], []
+
+    def work(r):
+        try:
+            with capi.Context(700, 64, 0, r, 2, uid) as ctx:
+                ctx.set_params(6.67e-11, 1e-3)
+                ctx.upload_aos(b)
+                norms = ctx.step_embedded(t["a"], t["b"], t["b_err"], 5e-3)
+                fin = ctx.download_aos()
+                ctx.step_undo()
+                back = ctx.download_aos()
+                ctx.step_rk(t["a"], t["b"], 5e-3, 1)
+                again = ctx.download_aos()
+                out[r] = (norms, fin, back, again)
+        except Exception as ex:                                # noqa: BLE001
+            errs.append((r, repr(ex)))
+    th = [threading.Thread(target=work, args=(r,)) for r in range(2)]
+    [x.start() for x in th]
+    [x.join(600) for x in th]
+    assert not errs and all(o is not None for o in out), errs
+    for norms, fin, back, again in out:
+        assert np.allclose(norms[:2], werr[:2], rtol=1e-4) and np.allclose(norms[2:], werr[2:], rtol=1e-12)
+        check_state(fin, want, b, 1e-10)
+        assert np.array_equal(back, b) and np.array_equal(again, fin)
+    assert np.array_equal(out[0][0], out[1][0])                # all-reduced: identical on every rank

@@ -47,7 +47,7 @@ namespace emu {
 
 struct Fiber {
 	ucontext_t ctx;
-	std::vector<unsigned char> stack;
+	unsigned char* stack = nullptr;	 // from the per-thread pool below (never zero-filled)
 	dim3 tid;
 	bool done = false;
 	unsigned long long sync_epoch = 0;	// __syncthreads passed so far
@@ -69,6 +69,11 @@ struct Cta {
 };
 
 // all emulation state is per OS thread: rank threads of one process may emulate concurrently
+constexpr size_t STACK_BYTES = 128 * 1024;
+inline std::vector<unsigned char*>& stack_pool() {
+	static thread_local std::vector<unsigned char*> pool;	// kept for the life of the thread
+	return pool;
+}
 inline Cta*& cta() { static thread_local Cta* c = nullptr; return c; }
 inline Fiber*& cur() { static thread_local Fiber* f = nullptr; return f; }
 inline ucontext_t& sched_ctx() { static thread_local ucontext_t c; return c; }
@@ -149,10 +154,11 @@ inline void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function
 		for (unsigned t = 0; t < block.x; ++t) {
 			Fiber& f = c.fibers[t];
 			f.tid = dim3(t);
-			f.stack.resize(256 * 1024);
+			if (stack_pool().size() <= t) stack_pool().push_back(static_cast<unsigned char*>(malloc(STACK_BYTES)));
+			f.stack = stack_pool()[t];
 			getcontext(&f.ctx);
-			f.ctx.uc_stack.ss_sp = f.stack.data();
-			f.ctx.uc_stack.ss_size = f.stack.size();
+			f.ctx.uc_stack.ss_sp = f.stack;
+			f.ctx.uc_stack.ss_size = STACK_BYTES;
 			f.ctx.uc_link = &sched_ctx();
 			makecontext(&f.ctx, (void (*)())trampoline, 0);
 		}
@@ -235,6 +241,12 @@ using std::min;
 inline void __nanosleep(unsigned) { emu::yield(); }
 inline void __threadfence_system() {}
 
+template <typename T>
+inline T atomicMax(T* p, T v) {
+	const T old = *p;
+	if (v > old) *p = v;
+	return old;
+}
 template <typename T>
 inline T atomicAdd(T* p, T v) {
 	const T old = *p;

@@ -41,10 +41,14 @@ uint64_t g_next_id = 1;
 size_t elem_size(int dt) { return dt == 8 ? 8 : dt == 7 ? 4 : 1; }
 
 template <typename T>
-void sum_into(T* out, const std::vector<const void*>& send, size_t offset, size_t count) {
+void sum_into(T* out, const std::vector<const void*>& send, size_t offset, size_t count, int op = 0) {
 	for (size_t k = 0; k < count; ++k) {
-		T s = 0;
-		for (const void* p : send) s += static_cast<const T*>(p)[offset + k];  // rank order: deterministic
+		T s = static_cast<const T*>(send[0])[offset + k];
+		for (size_t r = 1; r < send.size(); ++r) {	// rank order: deterministic
+			const T v = static_cast<const T*>(send[r])[offset + k];
+			if (op == 0) s += v;
+			else if (v > s || v != v) s = v;  // ncclMax (NaN wins, as it must stay visible)
+		}
 		out[k] = s;
 	}
 }
@@ -106,13 +110,13 @@ int ncclAllGather(const void* send, void* recv, size_t count, int dt, ncclComm_t
 }
 
 int ncclAllReduce(const void* send, void* recv, size_t count, int dt, int op, ncclComm_t c, void*) {
-	if (op != 0 || (dt != 8 && dt != 7)) return 4;
+	if ((op != 0 && op != 2) || (dt != 8 && dt != 7)) return 4;	 // ncclSum, ncclMax
 	Group* g = c->g;
 	g->send[c->rank] = send;
 	g->barrier();
 	std::vector<char> tmp(count * elem_size(dt));
-	if (dt == 8) sum_into(reinterpret_cast<double*>(tmp.data()), g->send, 0, count);
-	else sum_into(reinterpret_cast<float*>(tmp.data()), g->send, 0, count);
+	if (dt == 8) sum_into(reinterpret_cast<double*>(tmp.data()), g->send, 0, count, op);
+	else sum_into(reinterpret_cast<float*>(tmp.data()), g->send, 0, count, op);
 	g->barrier();  // everyone has read every send buffer: in-place results may be written
 	memcpy(recv, tmp.data(), tmp.size());
 	g->barrier();
