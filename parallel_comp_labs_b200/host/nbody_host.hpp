@@ -34,6 +34,7 @@
 #include <vector>
 
 #include "nbody_b200.h"
+#include "nbody_tableaux.hpp"
 
 namespace nbody_host {
 
@@ -346,12 +347,15 @@ struct RunOptions {
 	long out_every = 1;
 	long max_steps = 0;
 	long variant = -1;
+	std::string tableau;	 // "" = `scheme`; else a name from nbody_tableaux.hpp (nbody_step_rk)
+	double adaptive_rtol = 0;  // > 0: step-size control over the embedded pair `tableau`, tau = first step
+	double adaptive_atol = 0;
 	bool pair_symmetry = false;	 // opt-in: evaluate each pair once (one GPU), see include/nbody_b200.h
 	bool report = false;
 };
 
 struct RunResult {
-	long steps = 0;
+	long steps = 0, rejected = 0;
 	double wall_s = 0, loop_s = 0, gpu_ms = 0, writer_busy_s = 0;  // loop_s: until the GPU is idle;
 	// wall_s additionally includes draining the trajectory writer (the last row's formatting)
 	double interactions = 0;
@@ -437,15 +441,51 @@ class Solver_N_body {
 			// The reference's loop, in T: ode_RK2_MPI.hpp:65,72,98-99
 			T t = sys.t_start + sys.tau;
 			long steps = 0;
+			const nbody_host::Tableau* tab = nullptr;
+			std::vector<double> tab_a;
+			if (!opt.tableau.empty()) {
+				tab = nbody_host::find_tableau(opt.tableau);
+				if (!tab) { error = "unknown tableau " + opt.tableau; nbody_destroy(ctx); return; }
+				if (opt.adaptive_rtol > 0 && !tab->embedded) {
+					error = "tableau " + opt.tableau + " has no embedded companion"; nbody_destroy(ctx); return;
+				}
+				tab_a = tab->flat_a();
+			}
+			if (tab && opt.adaptive_rtol > 0) {
+				// Step-size control (not in the reference): rows are written at the accepted times.
+				// Every rank sees the same all-reduced norms, so all take the same decisions.
+				double time = (double)sys.t_start, tau = (double)sys.tau;
+				const int q = tab->order < tab->err_order ? tab->order : tab->err_order;
+				const long cap = opt.max_steps > 0 ? opt.max_steps : 100000000L;
+				while (time < (double)sys.t_final && steps < cap) {
+					if (tau > (double)sys.t_final - time) tau = (double)sys.t_final - time;
+					double nrm[4];
+					if (nbody_step_embedded(ctx, tab->stages, tab_a.data(), tab->b, tab->b_err, tau, nrm))
+						return fail("step_embedded");
+					const double er = nrm[0] / (opt.adaptive_atol + opt.adaptive_rtol * nrm[2]);
+					const double ev = nrm[1] / (opt.adaptive_atol + opt.adaptive_rtol * nrm[3]);
+					const double err = er > ev ? er : ev;
+					if (!(err == err)) { error = "non-finite error estimate"; nbody_destroy(ctx); return; }
+					if (err <= 1.0) {
+						time += tau;
+						++steps;
+						if (writer && (steps % opt.out_every == 0)) writer->push(time);
+					} else {
+						if (nbody_step_undo(ctx)) return fail("step_undo");
+						++res.rejected;
+					}
+					tau *= nbody_host::controller_factor(err, q);
+				}
+			} else
 			while (true) {
-				if (nbody_step(ctx, opt.scheme, (double)sys.tau, 1)) return fail("step");
-				nbody_timing tm;
+				if (tab ? nbody_step_rk(ctx, tab->stages, tab_a.data(), tab->b, (double)sys.tau, 1)
+						: nbody_step(ctx, opt.scheme, (double)sys.tau, 1))
+					return fail("step");
 				++steps;
 				if (writer && (steps % opt.out_every == 0)) writer->push((double)t);
 				if (opt.max_steps > 0 && steps >= opt.max_steps) break;
 				if (t > sys.t_final) break;
 				t += sys.tau;
-				(void)tm;
 			}
 			if (nbody_sync(ctx)) return fail("sync");
 			res.loop_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
@@ -455,8 +495,8 @@ class Solver_N_body {
 			}
 			res.wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
 			res.steps = steps;
-			const int stages = opt.scheme == NBODY_RK2 ? 2 : 4;
-			res.interactions = (double)stages * (double)n * (double)n * (double)steps;
+			const int stages = tab ? tab->stages : (opt.scheme == NBODY_RK2 ? 2 : 4);
+			res.interactions = (double)stages * (double)n * (double)n * (double)(steps + res.rejected);
 		}
 		if (opt.report && nbody_energy(ctx, &res.e_kin1, &res.e_pot1)) return fail("energy");
 		std::vector<Body<T>> fin(n);

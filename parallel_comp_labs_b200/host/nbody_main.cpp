@@ -42,12 +42,15 @@ void usage() {
 	std::puts(
 		"nbody_b200 --input FILE [--system default_test|random] [--tau 0.1] [--t-start 0]\n"
 		"           [--t-final 20|1] [--eps 1e-6] [--G 6.67e-11] [--precision 64|32]\n"
-		"           [--scheme rk2|rk4] [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
+		"           [--scheme rk2|rk4|euler|midpoint|heun|ralston|kutta3|rk38|bs23|rkf45|cashkarp|dopri5]\n"
+		"           [--adaptive-rtol R [--adaptive-atol A]]   (step-size control, embedded pairs; --tau = first step)\n"
+		"           [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
 		"           [--output-folder ../output] [--variant -1] [--pair-symmetry] [--report]\n"
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
 		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
-		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)");
+		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)\n"
+		"nbody_b200 --list-tableaux   (the schemes --scheme accepts, with their coefficients; no GPU)");
 }
 
 template <typename T>
@@ -72,7 +75,18 @@ int run(const Args& a) {
 	sys.N_bodies = (int)sys.traj_init.size();
 
 	RunOptions opt;
-	opt.scheme = a.str("scheme", "rk2") == "rk4" ? NBODY_RK4 : NBODY_RK2;
+	const std::string scheme = a.str("scheme", "rk2");
+	opt.scheme = scheme == "rk4" ? NBODY_RK4 : NBODY_RK2;
+	if (scheme != "rk2" && scheme != "rk4") {  // a named tableau (nbody_tableaux.hpp)
+		if (!find_tableau(scheme)) {
+			std::cerr << "unknown --scheme " << scheme << std::endl;
+			return 2;
+		}
+		opt.tableau = scheme;
+	}
+	opt.adaptive_rtol = a.num("adaptive-rtol", 0);
+	opt.adaptive_atol = a.num("adaptive-atol", 0);
+	if (opt.adaptive_rtol > 0 && opt.tableau.empty()) opt.tableau = "dopri5";
 	opt.n_gpus = (int)a.num("gpus", 1);
 	opt.flavour = a.str("flavour", "lab4");
 	opt.traj_path = a.str("traj-out", "");
@@ -105,11 +119,12 @@ int run(const Args& a) {
 		const RunResult& r = solver.result;
 		const double e0 = r.e_kin0 + r.e_pot0, e1 = r.e_kin1 + r.e_pot1;
 		std::printf(
-			"{\"n\": %zu, \"precision\": %d, \"scheme\": \"%s\", \"gpus\": %d, \"steps\": %ld, "
+			"{\"n\": %zu, \"precision\": %d, \"scheme\": \"%s\", \"gpus\": %d, \"steps\": %ld, \"rejected\": %ld, "
 			"\"wall_s\": %.6f, \"loop_s\": %.6f, \"G_interactions_per_s\": %.3f, \"writer_busy_s\": %.6f, "
 			"\"energy0\": %.17g, \"energy1\": %.17g, \"energy_drift\": %.3e}\n",
-			sys.traj_init.size(), (int)(8 * sizeof(T)), opt.scheme == NBODY_RK4 ? "rk4" : "rk2",
-			opt.n_gpus, r.steps, r.wall_s, r.loop_s, r.interactions / r.loop_s / 1e9, r.writer_busy_s, e0,
+			sys.traj_init.size(), (int)(8 * sizeof(T)),
+			!opt.tableau.empty() ? opt.tableau.c_str() : opt.scheme == NBODY_RK4 ? "rk4" : "rk2",
+			opt.n_gpus, r.steps, r.rejected, r.wall_s, r.loop_s, r.interactions / r.loop_s / 1e9, r.writer_busy_s, e0,
 			e1,
 			e0 != 0 ? std::fabs(e1 - e0) / std::fabs(e0) : 0.0);
 	}
@@ -146,6 +161,16 @@ int main(int argc, char** argv) {
 		k = k.substr(2);
 		if (i + 1 < argc && std::strncmp(argv[i + 1], "--", 2) != 0) a.kv[k] = argv[++i];
 		else a.kv[k] = "1";
+	}
+	if (a.has("list-tableaux")) {  // name stages order err_order | a (row-major) | b | b_err; no GPU
+		for (const Tableau& t : tableaux()) {
+			std::printf("%s %d %d %d", t.name, t.stages, t.order, t.embedded ? t.err_order : 0);
+			for (double v : t.flat_a()) std::printf(" %.17g", v);
+			for (int j = 0; j < t.stages; ++j) std::printf(" %.17g", t.b[j]);
+			for (int j = 0; j < t.stages; ++j) std::printf(" %.17g", t.embedded ? t.b_err[j] : 0.0);
+			std::printf("\n");
+		}
+		return 0;
 	}
 	if (a.has("generate")) {  // --generate uniform|plummer --n N [--seed S] --generate-out FILE
 		const std::size_t n = (std::size_t)a.num("n", 0);

@@ -359,3 +359,60 @@ def test_emulated_abi_embedded_step_on_two_ranks(oracle):
         check_state(fin, want, b, 1e-10)
         assert np.array_equal(back, b) and np.array_equal(again, fin)
     assert np.array_equal(out[0][0], out[1][0])                # all-reduced: identical on every rank
+
+
+# ------------------------------------------------------------------ the C++ host driver
+@pytest.fixture(scope="module")
+def emulated_driver(emulated_library):
+    """bin/nbody_b200's source linked with the emulated library instead of libnbody_b200.so."""
+    out = os.path.join(tempfile.mkdtemp(prefix="drvemu"), "nbody_b200_emu")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-Wno-unknown-pragmas", "-w",
+                    "-I" + os.path.join(ROOT, "include"),
+                    "-I" + os.path.join(ROOT, "parallel_comp_labs_b200", "host"), "-o", out,
+                    os.path.join(ROOT, "parallel_comp_labs_b200", "host", "nbody_main.cpp"),
+                    os.path.join(ROOT, "tests", "tools", "nbody_capi_emu.cpp"), "-ldl", "-lpthread"],
+                   check=True)
+    return out
+
+
+def _write_input(path, bodies):
+    with open(path, "w") as f:
+        f.write(f"{bodies.shape[0]}\n")
+        for b in bodies:
+            f.write(" ".join("%.17g" % x for x in b) + "\n")
+
+
+def test_emulated_cxx_driver_reference_run_and_schemes(emulated_driver, golden, tmp_path):
+    """The lab's own run (4-body file, RK2, tau = 0.1) through the C++ driver: trajectory CSV in the
+    lab_4 flavour against the rows the reference build wrote; then 2 rank threads (NCCL stand-in),
+    a named tableau, and the step-size controller."""
+    inp = str(tmp_path / "4body.txt")
+    _write_input(inp, golden["body4"])
+    ref = golden["ref_rk2_4body_0100"]
+    env = dict(os.environ)                                    # NBODY_NCCL_LIB set by the fixture
+
+    def run(*extra, steps=12):
+        traj = str(tmp_path / f"traj{len(os.listdir(tmp_path))}.csv")
+        r = subprocess.run([emulated_driver, "--system", "default_test", "--input", inp, "--tau", "0.1",
+                            "--t-final", "20", "--max-steps", str(steps), "--traj-out", traj,
+                            "--timing-out", str(tmp_path / "timing.csv"), *extra],
+                           capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stdout + r.stderr
+        lines = open(traj).read().splitlines()
+        rows = np.array([[float(x) for x in ln.split(";")[:-1]] for ln in lines[1:]])
+        return lines[0], rows, r.stdout
+
+    header, rows, _ = run()
+    assert header + "\n" == lab.LAB4_HEADER and rows.shape == (13, 13)   # t_start row + 12 steps
+    assert rel_inf(rows, ref[:13]) < 1e-12
+    _, rows2, _ = run("--gpus", "2", "--pair-symmetry")
+    assert rel_inf(rows2, ref[:13]) < 1e-12
+    _, rows_mid, _ = run("--scheme", "midpoint")              # the same scheme as a tableau
+    assert rel_inf(rows_mid, ref[:13]) < 1e-12
+    _, rows_dp, out = run("--scheme", "dopri5", "--report", steps=20)
+    assert np.abs(rows_dp[20, 1:4] - golden["traj1"][20, 1:4]).max() < 2e-5
+    assert '"scheme": "dopri5"' in out
+    _, rows_ad, out = run("--adaptive-rtol", "1e-10", "--t-final", "2", "--report", steps=0)
+    assert abs(rows_ad[-1, 0] - 2.0) < 1e-12 and '"rejected"' in out
+    exact = np.array([np.interp(rows_ad[-1, 0], golden["traj1"][:, 0], golden["traj1"][:, k]) for k in (1, 2, 3)])
+    assert np.abs(rows_ad[-1, 1:4] - exact).max() < 2e-5

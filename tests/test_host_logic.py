@@ -222,3 +222,25 @@ def test_pair_symmetric_schedule_covers_every_pair_once(oracle):
                 assert (cov == 1).all(), (n, ipt, slices, um, int(cov.min()), int(cov.max()))
                 want = oracle.rhs(b)[:, 4:7]
                 assert np.abs(acc - want).max() <= 1e-12 * max(np.abs(want).max(), 1e-300)
+
+
+def test_cxx_tableaux_match_python_table():
+    """nbody_tableaux.hpp (C++ driver) and tableaux.py (Python mirror) hold the same schemes."""
+    from parallel_comp_labs_b200 import tableaux
+    exe = os.path.join(ROOT, "parallel_comp_labs_b200", "bin", "nbody_b200")
+    out = subprocess.run([exe, "--list-tableaux"], capture_output=True, text=True, check=True).stdout
+    seen = set()
+    for line in out.splitlines():
+        f = line.split()
+        name, s, order, err_order = f[0], int(f[1]), int(f[2]), int(f[3])
+        v = np.array([float(x) for x in f[4:]])
+        assert v.size == s * s + 2 * s
+        t = tableaux.TABLEAUX[name]
+        assert t["order"] == order and (t["err_order"] or 0) == err_order
+        assert np.array_equal(v[:s * s].reshape(s, s), t["a"])
+        assert np.array_equal(v[s * s:s * s + s], t["b"])
+        if t["b_err"] is not None:
+            assert np.array_equal(v[s * s + s:], t["b_err"])
+        assert tableaux.check_order_conditions(name) < 1e-14
+        seen.add(name)
+    assert seen == set(tableaux.TABLEAUX)

@@ -2,7 +2,7 @@
 // parallel_comp_labs_b200/csrc/nbody_capi.cu uses, as plain host code, so that the whole C ABI
 // can be built by g++ (tests/tools/nbody_capi_emu.cpp) and its host logic -- launch plans,
 // buffer sizing, stage sequencing, snapshot ring, CUDA-graph replay -- runs in the CPU suite with
-// the kernels executed by cuda_emu.h.  One "device", sm_100-like, 2 SMs; device memory is host
+// the kernels executed by cuda_emu.h.  Eight identical "devices", sm_100-like, 2 SMs each; device memory is host
 // memory filled with 0xFF (NaN) so reads of never-written rows show up; streams execute in issue
 // order at once; a capturing stream records closures that cudaGraphLaunch replays.
 // Never linked into the product, which has no CPU path.
@@ -56,7 +56,7 @@ enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpy
 #define NB_LAUNCH(kern, grid, block, smem, stream, ...) \
 	emu_rt::enqueue(stream, [=] { emu::launch(grid, block, smem, [&] { kern(__VA_ARGS__); }); })
 
-inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return cudaSuccess; }
+inline cudaError_t cudaGetDeviceCount(int* n) { *n = 8; return cudaSuccess; }  // rank threads name devices 0..7
 inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp* p, int) {
 	memset(p, 0, sizeof(*p));
 	strcpy(p->name, "emulated sm_100 (CPU test build)");
