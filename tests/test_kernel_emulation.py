@@ -114,3 +114,18 @@ def test_emulated_pair_symmetric_kernel_on_several_ranks(emu_lib, oracle):
                                  acc.ctypes.data, err, 256)
         assert rc == 0, (rc, err.value.decode())
         assert rel_inf(acc, oracle.rhs(b)[:, 4:7]) < 1e-14
+
+
+def test_emulation_catches_deliberate_defects():
+    """The checker checked: a ring kernel built on the product's mbarrier / bulk-copy helpers runs
+    clean, and its three defective twins are reported -- a stage refilled before every reader has
+    passed a barrier, a lane that skips a warp collective, a wait on a stage that was never armed."""
+    out = os.path.join(tempfile.mkdtemp(prefix="emuself"), "libemuself.so")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-Wno-unknown-pragmas", "-shared", "-fPIC", "-o", out,
+                    os.path.join(ROOT, "tests", "tools", "emu_selftest.cpp")], check=True)
+    L = C.CDLL(out)
+    L.selftest.restype = C.c_char_p
+    assert L.selftest(0) == b""
+    assert b"may still be reading" in L.selftest(1)
+    assert b"deadlock" in L.selftest(2)
+    assert b"deadlock" in L.selftest(3)

@@ -74,6 +74,13 @@ inline std::vector<unsigned char*>& stack_pool() {
 	static thread_local std::vector<unsigned char*> pool;	// kept for the life of the thread
 	return pool;
 }
+inline uint64_t& sched_seed() {
+	static thread_local uint64_t seed = [] {
+		const char* e = getenv("EMU_SCHED_SEED");
+		return e ? (uint64_t)strtoull(e, nullptr, 0) * 0x9E3779B97F4A7C15ull + 1 : (uint64_t)0;
+	}();
+	return seed;
+}
 inline Cta*& cta() { static thread_local Cta* c = nullptr; return c; }
 inline Fiber*& cur() { static thread_local Fiber* f = nullptr; return f; }
 inline ucontext_t& sched_ctx() { static thread_local ucontext_t c; return c; }
@@ -166,7 +173,21 @@ inline void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function
 		for (;;) {
 			const unsigned long long before = c.progress;
 			unsigned alive = 0;
-			for (Fiber& f : c.fibers) {
+			// EMU_SCHED_SEED=<n>: visit the threads in a fresh pseudo-random order on every sweep
+			// instead of 0,1,2,...: which thread reaches a rendezvous first, and how far thread 0
+			// (the producer of the bulk copies) runs ahead of its consumers, then varies from run
+			// to run -- a missing barrier shows up as a wrong result or a failed ring check
+			std::vector<unsigned> order(c.fibers.size());
+			for (unsigned t = 0; t < order.size(); ++t) order[t] = t;
+			if (sched_seed()) {
+				uint64_t& x = sched_seed();
+				for (size_t t = order.size(); t > 1; --t) {
+					x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+					std::swap(order[t - 1], order[(size_t)(x % t)]);
+				}
+			}
+			for (unsigned t : order) {
+				Fiber& f = c.fibers[t];
 				if (f.done) continue;
 				++alive;
 				cur() = &f;
