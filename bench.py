@@ -194,6 +194,10 @@ def workload_config(args, tau, eps, variant):
             "parallelism": (f"i-rows over {args.gpus} GPU(s), peer-pull exchange: remote j-tiles "
                             f"fetched from the peers' HBM by the force kernel's bulk-async copies"
                             if getattr(args, "p2p", 0) and args.gpus > 1 else
+                            f"pair-symmetric kernel (opt-in): the blocks of one global schedule split "
+                            f"over {args.gpus} GPU(s); per RK stage an NCCL all-gather of the packed "
+                            f"positions (waited for) and a reduce-scatter of the j-side sums"
+                            if getattr(args, "pair_symmetry", 0) else
                             f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
                             f"per RK stage overlapped with the local-tile force launch"),
             "kernel_variant": variant}
