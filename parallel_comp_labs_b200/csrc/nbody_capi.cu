@@ -552,15 +552,15 @@ int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
 int p2p_publish(nbody_ctx* ctx, StageBuf buf) {
 	ctx->epoch++;
 	ctx->epoch_of[buf] = ctx->epoch;
-	NB_LAUNCH(p2p_signal_kernel, dim3(1), dim3(32), 0, ctx->sc, ctx->d_peer_flags, ctx->world, ctx->rank,
-			  ctx->epoch);
+	NB_LAUNCH(p2p_signal_kernel, dim3(1), dim3(32), 0, ctx->sc,
+			  ctx->d_peer_flags, ctx->world, ctx->rank, ctx->epoch);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
 }
 int p2p_wait(nbody_ctx* ctx, StageBuf buf) {
-	NB_LAUNCH(p2p_wait_kernel, dim3(1), dim3(32), 0, ctx->sc, ctx->d_flags, ctx->world, ctx->rank,
-			  ctx->epoch_of[buf]);
+	NB_LAUNCH(p2p_wait_kernel, dim3(1), dim3(32), 0, ctx->sc,
+			  ctx->d_flags, ctx->world, ctx->rank, ctx->epoch_of[buf]);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
@@ -1117,12 +1117,15 @@ int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
 	detect_uniform_mass(ctx, bodies, 7);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		NB_LAUNCH(pack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, (const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
-			ctx->own0, ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
+		NB_LAUNCH(pack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+				  ctx->own0, ctx->own_pad, ctx->unimass ? 1e150 : 0.,
+				  ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		NB_LAUNCH(pack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, (const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
-			ctx->own0, ctx->own_pad, ctx->unimass ? 1e18f : 0.f,
-			ctx->unimass ? (float)ctx->uniform_mass : 0.f);
+		NB_LAUNCH(pack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->vel_n, (unsigned)ctx->n, ctx->n_pad,
+				  ctx->own0, ctx->own_pad, ctx->unimass ? 1e18f : 0.f,
+				  ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaStreamSynchronize(ctx->sc));	 // the host buffer is borrowed for the call only
@@ -1149,11 +1152,15 @@ int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* 
 	detect_uniform_mass(ctx, m, 1);
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
-		NB_LAUNCH(pack_soa_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, (const double*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
-			ctx->own_pad, ctx->unimass ? 1e150 : 0., ctx->unimass ? ctx->uniform_mass : 0.);
+		NB_LAUNCH(pack_soa_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const double*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad,
+				  ctx->own0, ctx->own_pad, ctx->unimass ? 1e150 : 0.,
+				  ctx->unimass ? ctx->uniform_mass : 0.);
 	else
-		NB_LAUNCH(pack_soa_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, (const float*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad, ctx->own0,
-			ctx->own_pad, ctx->unimass ? 1e18f : 0.f, ctx->unimass ? (float)ctx->uniform_mass : 0.f);
+		NB_LAUNCH(pack_soa_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const float*)d, dr, dv, ctx->Y, ctx->P, ctx->vel_n, (unsigned)n, ctx->n_pad,
+				  ctx->own0, ctx->own_pad, ctx->unimass ? 1e18f : 0.f,
+				  ctx->unimass ? (float)ctx->uniform_mass : 0.f);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaStreamSynchronize(ctx->sc));
@@ -1433,11 +1440,11 @@ int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
 	if ((rc = ensure_y_gathered(ctx))) return rc;
 	const unsigned g = ((unsigned)ctx->n + 255) / 256;
 	if (ctx->prec == 64)
-		NB_LAUNCH(snapshot_pack_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, (double*)ctx->snap_dev[slot],
-															 (unsigned)ctx->n);
+		NB_LAUNCH(snapshot_pack_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+				  ctx->Y, (double*)ctx->snap_dev[slot], (unsigned)ctx->n);
 	else
-		NB_LAUNCH(snapshot_pack_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, (float*)ctx->snap_dev[slot],
-															(unsigned)ctx->n);
+		NB_LAUNCH(snapshot_pack_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+				  ctx->Y, (float*)ctx->snap_dev[slot], (unsigned)ctx->n);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaEventRecord(ctx->e_snap, ctx->sc));
@@ -1496,11 +1503,11 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
 	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes + 64));
 	const unsigned g = ((unsigned)ctx->n + 255) / 256;
 	if (ctx->prec == 64)
-		NB_LAUNCH(unpack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, vel, (double*)ctx->d_aos,
-														  (unsigned)ctx->n);
+		NB_LAUNCH(unpack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+				  ctx->Y, vel, (double*)ctx->d_aos, (unsigned)ctx->n);
 	else
-		NB_LAUNCH(unpack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, vel, (float*)ctx->d_aos,
-														 (unsigned)ctx->n);
+		NB_LAUNCH(unpack_aos_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+				  ctx->Y, vel, (float*)ctx->d_aos, (unsigned)ctx->n);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaMemcpyAsync(bodies, ctx->d_aos, bytes, cudaMemcpyDeviceToHost, ctx->sc));
@@ -1519,17 +1526,17 @@ int nbody_diagnostics(nbody_ctx* ctx, double out[9]) {
 		const unsigned g = (ctx->own_real + 255) / 256;
 		const unsigned gm = std::min(g, 4u * (unsigned)ctx->n_sm);
 		if (ctx->prec == 64) {
-			NB_LAUNCH(energy_kernel<double>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, (unsigned)ctx->n,
-														  ctx->own0, ctx->own_real, ctx->eps,
-														  ctx->G, ctx->d_energy);
-			NB_LAUNCH(moments_kernel<double>, dim3(gm), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, ctx->own0,
-															ctx->own_real, ctx->d_energy + 2);
+			NB_LAUNCH(energy_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, (unsigned)ctx->n, ctx->own0, ctx->own_real, ctx->eps, ctx->G,
+					  ctx->d_energy);
+			NB_LAUNCH(moments_kernel<double>, dim3(gm), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, ctx->own0, ctx->own_real, ctx->d_energy + 2);
 		} else {
-			NB_LAUNCH(energy_kernel<float>, dim3(g), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, (unsigned)ctx->n,
-														 ctx->own0, ctx->own_real, ctx->eps,
-														 ctx->G, ctx->d_energy);
-			NB_LAUNCH(moments_kernel<float>, dim3(gm), dim3(256), 0, ctx->sc, ctx->Y, ctx->vel_n, ctx->own0,
-														   ctx->own_real, ctx->d_energy + 2);
+			NB_LAUNCH(energy_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, (unsigned)ctx->n, ctx->own0, ctx->own_real, ctx->eps, ctx->G,
+					  ctx->d_energy);
+			NB_LAUNCH(moments_kernel<float>, dim3(gm), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, ctx->own0, ctx->own_real, ctx->d_energy + 2);
 		}
 		CK(cudaGetLastError());
 		ctx->tm.total_launches += 2;
@@ -1583,9 +1590,11 @@ int nbody_measure_fma_peak(int device, int precision, double ms_target, double* 
 	for (int pass = 0; pass < 8; ++pass) {
 		CK(cudaEventRecord(e0, 0));
 		if (precision == 64)
-			NB_LAUNCH(fma_peak_kernel<double>, dim3(blocks), dim3(threads), 0, 0, (double*)d, 0.999999, 1e-9, iters);
+			NB_LAUNCH(fma_peak_kernel<double>, dim3(blocks), dim3(threads), 0, 0,
+					  (double*)d, 0.999999, 1e-9, iters);
 		else
-			NB_LAUNCH(fma_peak_kernel<float>, dim3(blocks), dim3(threads), 0, 0, (float*)d, 0.9999f, 1e-5f, iters);
+			NB_LAUNCH(fma_peak_kernel<float>, dim3(blocks), dim3(threads), 0, 0,
+					  (float*)d, 0.9999f, 1e-5f, iters);
 		CK(cudaEventRecord(e1, 0));
 		CK(cudaEventSynchronize(e1));
 		CK(cudaGetLastError());
