@@ -152,7 +152,10 @@ int nbody_step_tableau(nbody_ctx* ctx, int n_stages, const double* a_sub /* n_st
  * rule of ode_RK2_MPI.hpp:72-92).  All stage derivatives of the owned rows stay resident;
  *   k_s = f(y + tau sum_{j<s} a[s][j] k_j),   y += tau sum_s b[s] k_s.
  * a: n_stages x n_stages, row-major, only the strictly lower triangle is read; b: n_stages.
- * Same RHS kernels and exchange as nbody_step; one fused stage kernel per stage. */
+ * Same RHS kernels and exchange as nbody_step; one fused stage kernel per stage.  A force
+ * evaluation whose result is still resident is not repeated: "first same as last" tableaux
+ * (a[s-1][j] == b[j], b[s-1] == 0: Dormand-Prince, Bogacki-Shampine) reuse the last stage as the
+ * next step's first, and the step after nbody_step_undo reuses the rejected step's first stage. */
 int nbody_step_rk(nbody_ctx* ctx, int n_stages, const double* a, const double* b, double tau,
 				  long n_steps);
 

@@ -189,6 +189,7 @@ struct nbody_ctx {
 	double* d_norms = nullptr;
 	void *undo_Y = nullptr, *undo_vel = nullptr;
 	bool undo_valid = false;
+	int k0_slot = -1;  // slot of kr/kv that holds f(current state), or -1 (see enqueue_step_general)
 	uint64_t sym_pairs = 0;	 // pair evaluations of one symmetric RHS (cached with its key)
 	int sym_pairs_key = -1;
 	double* d_energy = nullptr;
@@ -655,6 +656,7 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 struct GenCoef {
 	int ns = 0;
 	bool want_err = false;
+	bool fsal = false;	// "first same as last": the last stage is f(y_{n+1}) = the next step's k_0
 	double a[NBODY_MAX_STAGES][NBODY_MAX_STAGES] = {};	// tau * a[s][j], j < s
 	double w[NBODY_MAX_STAGES] = {};					// tau * b[j]
 	double e[NBODY_MAX_STAGES] = {};					// tau * (b[j] - b_err[j])
@@ -662,7 +664,7 @@ struct GenCoef {
 
 template <typename T>
 int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, const GenCoef& k,
-						 int s) {
+						 int s, int k_from) {
 	if (ctx->own_real == 0) return NBODY_OK;
 	StageGenParams<T> g;
 	StageParams<T>& p = g.base;
@@ -692,6 +694,8 @@ int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, c
 	g.n_stages = k.ns;
 	g.last = s == k.ns - 1;
 	g.want_err = g.last && k.want_err;
+	g.k_from = k_from;
+	g.store_last = k.fsal ? 1 : 0;
 	g.norms = g.want_err ? ctx->d_norms : nullptr;
 	for (int j = 0; j < NBODY_MAX_STAGES; ++j) {
 		g.c[j] = j <= s ? (T)(g.last ? k.w[j] : k.a[s + 1][j]) : T(0);
@@ -768,11 +772,19 @@ int enqueue_step_general(nbody_ctx* ctx, const LaunchPlan& lp, const GenCoef& k)
 	for (int s = 0; s < k.ns; ++s) {
 		const StageBuf buf = stage_buf(ctx, s);
 		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
-		if ((rc = enqueue_forces(ctx, lp, buf, mode))) return rc;
+		// k_0 = f(y_n) may already be resident: the last stage of a "first same as last" scheme
+		// (Dormand-Prince, Bogacki-Shampine) or stage 0 of a step that was just undone
+		const int k_from = s == 0 ? ctx->k0_slot : -1;
+		if (k_from < 0) {
+			if ((rc = enqueue_forces(ctx, lp, buf, mode))) return rc;
+		} else if (mode == GATHER_PENDING_Y) {	// nobody else waits for the gather of y_n before
+			CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));	 // this step overwrites its block of Y
+			ctx->y_pending = false;
+		}
 		const bool last = s == k.ns - 1;
 		const StageBuf nxt = last ? BUF_Y : stage_buf(ctx, s + 1);
-		rc = ctx->prec == 64 ? launch_stage_general<double>(ctx, lp, buf_ptr(ctx, nxt), k, s)
-							 : launch_stage_general<float>(ctx, lp, buf_ptr(ctx, nxt), k, s);
+		rc = ctx->prec == 64 ? launch_stage_general<double>(ctx, lp, buf_ptr(ctx, nxt), k, s, k_from)
+							 : launch_stage_general<float>(ctx, lp, buf_ptr(ctx, nxt), k, s, k_from);
 		if (rc) return rc;
 		if (ctx->p2p && (rc = p2p_publish(ctx, nxt))) return rc;
 	}
@@ -782,6 +794,7 @@ int enqueue_step_general(nbody_ctx* ctx, const LaunchPlan& lp, const GenCoef& k)
 		if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;
 		ctx->y_pending = true;
 	}
+	ctx->k0_slot = (k.fsal && k.ns > 1) ? k.ns - 1 : -1;
 	return NBODY_OK;
 }
 
@@ -1037,6 +1050,7 @@ int nbody_set_params(nbody_ctx* ctx, double G, double eps) {
 	if (!(eps >= 0.)) return fail(ctx, NBODY_ERR_ARG, "eps must be >= 0");
 	ctx->G = G;
 	ctx->eps = eps;
+	ctx->k0_slot = -1;
 	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 	return NBODY_OK;
 }
@@ -1061,6 +1075,7 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		ctx->opt_unimass = value;
 	}
 	else return fail(ctx, NBODY_ERR_ARG, "unknown option " + k);
+	ctx->k0_slot = -1;
 	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 	return NBODY_OK;
 }
@@ -1094,6 +1109,7 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 
 static int upload_common(nbody_ctx* ctx) {
 	ctx->undo_valid = false;
+	ctx->k0_slot = -1;
 	if (ctx->P2)  // pad rows and masses of the second stage buffer
 		CK(cudaMemcpy(ctx->P2, ctx->P, (size_t)ctx->n_pad * 4 * ctx->esz, cudaMemcpyDeviceToDevice));
 	if (ctx->p2p) {	 // peers read this rank's block of Y from here on: publish it
@@ -1205,6 +1221,7 @@ int nbody_rhs(nbody_ctx* ctx, void* acc_host) {
 
 static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double tau, long n_steps) {
 	ctx->undo_valid = false;
+	ctx->k0_slot = -1;
 	if (n_steps < 0) return fail(ctx, NBODY_ERR_ARG, "n_steps < 0");
 	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "nbody_step before upload");
 	CK(cudaSetDevice(ctx->device));
@@ -1290,6 +1307,10 @@ static int make_gen_coef(nbody_ctx* ctx, int n_stages, const double* a, const do
 		k->w[s] = mul(tau, b[s]);
 		k->e[s] = b_err ? mul(tau, f64 ? b[s] - b_err[s] : (double)((float)b[s] - (float)b_err[s])) : 0.;
 	}
+	// first same as last: the last stage is evaluated at y_n + tau sum_j b[j] k_j = y_{n+1}
+	k->fsal = n_stages > 1 && b[n_stages - 1] == 0.0;
+	for (int j = 0; k->fsal && j + 1 < n_stages; ++j)
+		k->fsal = a[(n_stages - 1) * n_stages + j] == b[j];
 	return NBODY_OK;
 }
 
@@ -1300,6 +1321,7 @@ static int ensure_stage_store(nbody_ctx* ctx, int n_stages) {
 	if (ctx->kv) CK(cudaFree(ctx->kv));
 	ctx->kr = ctx->kv = nullptr;
 	ctx->k_stages = 0;
+	ctx->k0_slot = -1;
 	const size_t bytes = (size_t)n_stages * ctx->own_pad * 4 * ctx->esz;
 	CK(cudaMalloc(&ctx->kr, bytes));
 	CK(cudaMalloc(&ctx->kv, bytes));
@@ -1381,6 +1403,7 @@ int nbody_step_undo(nbody_ctx* ctx) {
 					   ctx->sc));
 	ctx->tm.steps_done -= 1;
 	ctx->undo_valid = false;
+	ctx->k0_slot = ctx->k_stages > 1 ? 0 : -1;	 // stage 0 of the rejected step was f(this state)
 	return NBODY_OK;
 }
 

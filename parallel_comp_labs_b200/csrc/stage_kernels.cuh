@@ -145,6 +145,9 @@ struct StageGenParams {
 	void* kv;				// V4[n_stages][own_pad]                    velocity part
 	double* norms;			// [4] or null
 	int s, n_stages, last, want_err;
+	int k_from;		 // >= 0 (stage 0 only): k_0 = f(y_n) is already resident in that slot of kr/kv
+					 // ("first same as last", or the retry of a rejected step): no force launch
+	int store_last;	 // keep the last stage's k as well (it is the next step's k_0)
 	T c[NBODY_MAX_STAGES_K2G];	// next-stage coefficients (j <= s), or the weights w on the last stage
 	T e[NBODY_MAX_STAGES_K2G];	// error weights (last stage of an embedded pair)
 };
@@ -165,21 +168,26 @@ __global__ void __launch_bounds__(256) stage_general_kernel(const StageGenParams
 	if (live) {
 		const vec4* apart = reinterpret_cast<const vec4*>(p.apart);
 		T ax = T(0), ay = T(0), az = T(0);
-		for (unsigned s = 0; s < p.n_slices; ++s) {
-			const vec4 q = apart[(size_t)s * p.apart_stride + i];
-			ax = add_rn(ax, q.x);
-			ay = add_rn(ay, q.y);
-			az = add_rn(az, q.z);
+		if (g.k_from >= 0) {  // the acceleration at y_n was computed by an earlier step
+			const vec4 q = reinterpret_cast<const vec4*>(g.kv)[(size_t)g.k_from * p.own_pad + i];
+			ax = q.x; ay = q.y; az = q.z;
+		} else {
+			for (unsigned s = 0; s < p.n_slices; ++s) {
+				const vec4 q = apart[(size_t)s * p.apart_stride + i];
+				ax = add_rn(ax, q.x);
+				ay = add_rn(ay, q.y);
+				az = add_rn(az, q.z);
+			}
+			if (p.aj) {
+				const T* gj = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
+				ax = add_rn(ax, gj[0]);
+				ay = add_rn(ay, gj[(size_t)p.aj_stride]);
+				az = add_rn(az, gj[2 * (size_t)p.aj_stride]);
+			}
+			ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
+			ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
+			az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);
 		}
-		if (p.aj) {
-			const T* gj = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
-			ax = add_rn(ax, gj[0]);
-			ay = add_rn(ay, gj[(size_t)p.aj_stride]);
-			az = add_rn(az, gj[2 * (size_t)p.aj_stride]);
-		}
-		ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
-		ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
-		az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);
 
 		vec4* Y = reinterpret_cast<vec4*>(p.Y);
 		vec4* P = reinterpret_cast<vec4*>(p.P);
@@ -193,7 +201,7 @@ __global__ void __launch_bounds__(256) stage_general_kernel(const StageGenParams
 		ks_r.w = T(0);
 		vec4 ks_v;
 		ks_v.x = ax; ks_v.y = ay; ks_v.z = az; ks_v.w = T(0);
-		if (!g.last) {	// later stages read it back; the last stage's k is used right here
+		if (!g.last || g.store_last) {	// later stages (or the next step) read it back
 			kr[(size_t)g.s * p.own_pad + i] = ks_r;
 			kv[(size_t)g.s * p.own_pad + i] = ks_v;
 		}

@@ -64,6 +64,14 @@ TABLEAUX = {
 }
 
 
+def is_fsal(name: str) -> bool:
+    """First same as last: the last stage is f(y_new), i.e. the next step's first stage.  The
+    library detects this from the coefficients and skips that force evaluation."""
+    t = TABLEAUX[name]
+    a, b = t["a"], t["b"]
+    return len(b) > 1 and b[-1] == 0.0 and bool(np.all(a[-1, :-1] == b[:-1]))
+
+
 def check_order_conditions(name: str) -> float:
     """Largest violation of the order conditions up to order 3 plus row-sum consistency (used by
     the CPU tests to guard the table against typos)."""

@@ -274,7 +274,8 @@ def test_emulated_abi_general_tableaux_vs_oracle(oracle):
             ctx.upload_aos(plu)
             ctx.step_rk(t["a"], t["b"], 2e-3, 2, sync=True)
             check_state(ctx.download_aos(), want, plu, 1e-10)
-            assert ctx.timing().force_launches == 2 * len(t["b"])
+            # "first same as last" schemes reuse the last stage as the next step's first
+            assert ctx.timing().force_launches == 2 * len(t["b"]) - (2 - 1) * tableaux.is_fsal(name)
     # the tableau path and the hard-wired RK4 agree (different rounding sequence, same scheme)
     t = tableaux.TABLEAUX["rk4"]
     with capi.Context(160, 64) as ctx:
@@ -315,6 +316,24 @@ def test_emulated_abi_embedded_step_undo_and_controller(oracle, golden):
             assert np.array_equal(ctx.download_aos(), plu)
             with pytest.raises(capi.NBodyError):
                 ctx.step_undo()                               # nothing left to undo
+    # force evaluations saved: "first same as last" after an accepted step, stage 0 after an undo
+    t = tableaux.TABLEAUX["dopri5"]
+    want, _ = oracle.rk_general(plu, t["a"], t["b"], 2e-3, 1, eps=1e-3, threads=8)
+    want, _ = oracle.rk_general(want, t["a"], t["b"], 1e-3, 1, eps=1e-3, threads=8)
+    with capi.Context(160, 64) as ctx:
+        ctx.set_params(6.67e-11, 1e-3)
+        ctx.upload_aos(plu)
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 2e-3)
+        assert ctx.timing().force_launches == 7
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 4e-3)
+        assert ctx.timing().force_launches == 6                   # k_0 = last stage of the step before
+        ctx.step_undo()
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 1e-3)       # the retry: k_0 = the rejected step's
+        assert ctx.timing().force_launches == 6
+        check_state(ctx.download_aos(), want, plu, 1e-10)
+        ctx.set_params(6.67e-11, 2e-3)                            # a different operator: nothing reusable
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 1e-3)
+        assert ctx.timing().force_launches == 7
     # the reference's 4-body problem with step-size control, against the accurate fixture solution
     b4 = golden["body4"]
     with capi.Context(4, 64) as ctx:

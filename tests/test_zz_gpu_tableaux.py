@@ -24,7 +24,7 @@ def test_tableau_vs_oracle(oracle, name):
         ctx.upload_aos(plu)
         ctx.step_rk(t["a"], t["b"], 2e-3, 3, sync=True)
         check_state(ctx.download_aos(), want, plu, 1e-10, steps=3)
-        assert ctx.timing().force_launches == 3 * len(t["b"])
+        assert ctx.timing().force_launches == 3 * len(t["b"]) - (3 - 1) * tableaux.is_fsal(name)
 
 
 def test_tableau_rk4_equals_hardwired_rk4_and_fp32(oracle):
@@ -64,6 +64,27 @@ def test_embedded_step_norms_and_undo(oracle, name):
         assert np.array_equal(ctx.download_aos(), plu)
         with pytest.raises(capi.NBodyError):
             ctx.step_undo()
+
+
+def test_force_evaluations_saved_by_fsal_and_after_undo(oracle):
+    t = tableaux.TABLEAUX["dopri5"]
+    plu = generators.plummer_bodies(1200, seed=14)
+    want, _ = oracle.rk_general(plu, t["a"], t["b"], 2e-3, 1, eps=1e-3, threads=8)
+    want, _ = oracle.rk_general(want, t["a"], t["b"], 1e-3, 1, eps=1e-3, threads=8)
+    with capi.Context(1200, 64) as ctx:
+        ctx.set_params(6.67e-11, 1e-3)
+        ctx.upload_aos(plu)
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 2e-3)
+        assert ctx.timing().force_launches == 7
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 4e-3)
+        assert ctx.timing().force_launches == 6       # k_0 = last stage of the step before
+        ctx.step_undo()
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 1e-3)
+        assert ctx.timing().force_launches == 6       # the retry reuses the rejected step's k_0
+        check_state(ctx.download_aos(), want, plu, 1e-10, steps=2)
+        ctx.set_params(6.67e-11, 2e-3)
+        ctx.step_embedded(t["a"], t["b"], t["b_err"], 1e-3)
+        assert ctx.timing().force_launches == 7
 
 
 def test_adaptive_controller_on_the_reference_4body_problem(golden):
