@@ -273,9 +273,14 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	if (v >= 0 && v < nv) return tab[v];
 	// auto: the first variant whose block (threads * i-bodies) divides the per-rank block of the
 	// partition -- on several GPUs the ranks must own whole blocks; 256-row blocks always fit
-	if (c->world > 1)
+	if (c->world > 1 && c->own_pad % (unsigned)(tab[0].threads * tab[0].ipt) != 0) {
 		for (int k = 0; k < nv; ++k)
 			if (c->own_pad % (unsigned)(tab[k].threads * tab[k].ipt) == 0) return tab[k];
+	}
+	// FP64 with general masses: 4 more live doubles (m_i); at 5 CTAs/SM (96 registers) ptxas spills
+	// inside the hot loop (tools/sym_sass_mix.py: 12.0 non-FP64 instructions per pair evaluation
+	// against 6.9 at 4 CTAs/SM), so take the 4-CTA build of the same blocking
+	if (c->prec == 64 && !c->unimass) return tab[1];
 	return tab[0];
 }
 
