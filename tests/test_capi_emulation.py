@@ -4,7 +4,7 @@ tests/tools/nbody_capi_emu.cpp is parallel_comp_labs_b200/csrc/nbody_capi.cu -- 
 source of libnbody_b200.so -- compiled by g++ against a stand-in CUDA runtime
 (tests/tools/cuda_rt_emu.h) with every kernel launch executed by the fiber emulation
 (tests/tools/cuda_emu.h).  The cases below are small versions of tests/test_gpu_parity.py and
-tests/test_zz_gpu_pair_symmetry.py: they drive the library's host logic (launch plans, buffer
+tests/test_zzz_gpu_pair_symmetry.py: they drive the library's host logic (launch plans, buffer
 sizing, stage sequencing, CUDA-graph replay, snapshot ring, uniform-mass detection, option
 handling) and the kernels' source through the same ctypes binding the GPU tests use, and compare
 with the oracle and the golden fixtures.  What they cannot show is anything about the hardware
