@@ -33,6 +33,38 @@
 
 namespace nbody {
 
+// K1s waits on the tile ring through a watchdog: a tile that has not landed 2 s after the wait
+// began is a protocol error (it cannot happen with the schedule in sym_schedule.h; the CPU
+// execution of this file checks the ring for deadlocks), and the kernel then traps so that the
+// host sees a launch failure instead of a hung device.  The fast path is the same single
+// try_wait as K1's mbar_wait; the timer is read only after 4096 failed polls.
+#ifndef NBODY_HOST_EMU
+__device__ __forceinline__ void mbar_wait_guarded(uint64_t* bar, uint32_t parity) {
+	uint32_t done, polls = 0;
+	unsigned long long t_begin = 0;
+	for (;;) {
+		asm volatile(
+			"{\n"
+			".reg .pred p;\n"
+			"mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+			"selp.u32 %0, 1, 0, p;\n"
+			"}\n"
+			: "=r"(done)
+			: "r"(smem_u32(bar)), "r"(parity)
+			: "memory");
+		if (done) return;
+		if ((++polls & 4095u) == 0) {
+			unsigned long long now;
+			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+			if (t_begin == 0) t_begin = now;
+			else if (now - t_begin > 2000000000ull) __trap();
+		}
+	}
+}
+#else
+inline void mbar_wait_guarded(uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); }
+#endif
+
 struct SymParams {
 	const void* pos;	 // V4[(jt_total + tpb) * TJ] positions {x,y,z,m}; rows >= n_pad unspecified
 	void* apart;		 // V4[n_slices][nb_own * BLOCK] i-side partial sums of the owned blocks
@@ -195,7 +227,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
 		for (unsigned t = 0; t < ntiles; ++t) {
 			const unsigned st = ring % STAGES;
-			mbar_wait(&full[st], (ring / STAGES) & 1u);
+			mbar_wait_guarded(&full[st], (ring / STAGES) & 1u);
 			const vec4* tile = tiles + (size_t)st * TJ;
 			bool diag;
 			const unsigned jt = sym_tile(p.nb, TPB, a, t0 + t, &diag);
