@@ -1,0 +1,62 @@
+#!/usr/bin/env bash
+# First GPU call of a round: everything that has only been run under CPU emulation so far
+# (K2g general tableaux, K1s pair-symmetric kernel) plus a fresh default bench line and the ncu
+# evidence for whichever force kernel wins.  One B200; every step has its own `timeout`, ncu runs
+# only after the same command has exited 0 without it, and all output lands in gpurun_out/.
+#
+#   gpurun --timeout 1500 -- 'bash tools/gpu_first_call.sh'
+#
+# Reading the result here: gpurun_out/first_call/*.log, *.json (one bench line each), *.csv.
+set -u
+cd "$(dirname "$0")/.."
+OUT=gpurun_out/first_call
+mkdir -p "$OUT"
+PY=python
+
+step() {  # step <name> <seconds> <command...>: run, log, record the exit code, never abort
+	local name=$1 secs=$2; shift 2
+	echo "== $name" | tee -a "$OUT/summary.txt"
+	timeout "$secs" "$@" > "$OUT/$name.log" 2>&1
+	local rc=$?
+	echo "   exit $rc" | tee -a "$OUT/summary.txt"
+	return $rc
+}
+bench_line() {  # bench_line <name> <seconds> <bench args...>: keeps the JSON line as <name>.json
+	local name=$1 secs=$2; shift 2
+	step "$name" "$secs" $PY bench.py "$@" && grep '^{' "$OUT/$name.log" | tail -1 > "$OUT/$name.json"
+}
+
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > "$OUT/gpu.txt" 2>&1
+
+# 1. parity: the whole -m gpu suite (the tableau and pair-symmetry files sort last)
+step pytest_gpu 900 $PY -m pytest tests -m gpu -x -q
+
+# 2. default path, the line the driver will take
+bench_line bench_default 400 --steps 2 --warmup 3
+
+# 3. pair-symmetric kernel: variants, general masses, FP32 (no CPU leg, no energy: kernel numbers)
+for v in 0 1 2 3 4; do
+	bench_line "bench_sym_v$v" 200 --pair-symmetry 1 --sym-variant $v --steps 2 --warmup 3 \
+		--no-cpu-baseline --no-energy
+done
+bench_line bench_sym_general 200 --pair-symmetry 1 --unimass 0 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_default_general 200 --unimass 0 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_sym_fp32 200 --pair-symmetry 1 --precision 32 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_sym_256k 200 --pair-symmetry 1 --bodies 262144 --steps 3 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_default_256k 200 --bodies 262144 --steps 3 --warmup 3 --no-cpu-baseline --no-energy
+
+# 4. ncu: launch list of the default bench command, then one full capture per force kernel at a
+#    size that keeps the replays short (N = 131072: ~16 ms per launch)
+if [ -s "$OUT/bench_default.json" ]; then
+	step ncu_launches 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+		--log-file "$OUT/launches.csv" $PY bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-energy
+	step ncu_full_default 600 ncu --set full --clock-control none --import-source on \
+		-k regex:force_kernel -c 1 -o "$OUT/force_kernel_131072" -f \
+		$PY tools/rhs_once.py --bodies 131072
+fi
+if [ -s "$OUT/bench_sym_v0.json" ]; then
+	step ncu_full_sym 600 ncu --set full --clock-control none --import-source on \
+		-k regex:force_sym_kernel -c 1 -o "$OUT/force_sym_kernel_131072" -f \
+		$PY tools/rhs_once.py --bodies 131072 --pair-symmetry 1
+fi
+cat "$OUT/summary.txt"
