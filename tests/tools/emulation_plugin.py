@@ -8,7 +8,9 @@ the driver's `pytest -m gpu` run, which goes through libnbody_b200.so on a real 
         -p no:timeout --deselect tests/test_gpu_parity.py::test_rhs_large_n_row_subsample \
         --deselect tests/test_gpu_parity.py::test_rk2_rk4_uniform20k_config
 
-(the two deselected cases are sized for a GPU: 262 144 and 20 000 bodies).  Tests that start the
+(the two deselected cases are sized for a GPU: 262 144 and 20 000 bodies; in
+tests/test_zzz_gpu_pair_symmetry.py deselect test_sym_large_n_row_subsample_and_momentum for the
+same reason).  Tests that start the
 compiled driver binary (tests/test_gpu_host_driver.py) or torchrun (tests/test_gpu_multi.py) need
 real devices and are not covered; tests/test_capi_emulation.py holds their emulated counterparts.
 EMU_SCHED_SEED=<n> randomises the order in which the emulated threads are visited."""
