@@ -158,3 +158,28 @@ def test_sym_mode_can_be_switched_on_a_live_context(oracle):
         a2 = ctx.rhs()
     assert np.array_equal(a0, a2)                      # the default path is deterministic
     assert rel_inf(a1, want) < TOL64_RHS and rel_inf(a0, want) < TOL64_RHS
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs >= 2 GPUs")
+def test_sym_two_ranks_match_oracle():
+    """Two ranks under torchrun (tests/tools/multi_check.py): every rank walks its blocks of the
+    one global schedule and the j-side sums are reduce-scattered over the ranks (NCCL)."""
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    env = dict(os.environ, NBODY_P2P="0", NBODY_PAIR_SYM="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                        "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",
+                        "29535", os.path.join(ROOT, "tests", "tools", "multi_check.py"), "3000"],
+                       capture_output=True, text=True, timeout=280, env=env)
+    assert r.returncode == 0 and "MULTI-GPU CHECK PASSED" in r.stdout, \
+        r.stdout[-3000:] + r.stderr[-3000:]
