@@ -33,7 +33,7 @@
 
 namespace nbody {
 
-// K1s waits on the tile ring through a watchdog: a tile that has not landed 2 s after the wait
+// K1s waits on the tile ring through a watchdog: a tile that has not landed 10 s after the wait
 // began is a protocol error (it cannot happen with the schedule in sym_schedule.h; the CPU
 // execution of this file checks the ring for deadlocks), and the kernel then traps so that the
 // host sees a launch failure instead of a hung device.  The fast path is the same single
@@ -57,7 +57,7 @@ __device__ __forceinline__ void mbar_wait_guarded(uint64_t* bar, uint32_t parity
 			unsigned long long now;
 			asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
 			if (t_begin == 0) t_begin = now;
-			else if (now - t_begin > 2000000000ull) __trap();
+			else if (now - t_begin > 10000000000ull) __trap();
 		}
 	}
 }
