@@ -117,11 +117,17 @@ __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz,
 
 // One strip: 32 rotation steps.  On return `loc` holds the strip's contribution to this thread's
 // i-bodies and (ajx,ajy,ajz) the strip's contribution to the j-body this lane STARTED with.
-template <typename T, int I, int ORD, bool UM, bool EXACT>
-__device__ __forceinline__ void sym_strip(const typename V4<T>::type pj, const T (&xi)[I],
+// ROT = 0: the j-body travels with its accumulator (6 shuffled doubles per step, no shared-memory
+// read in the loop).  ROT = 1: only the accumulator travels; lane l re-reads the j-body that is
+// visiting it, strip[(l + r + 1) & 31], from the staged tile (distinct consecutive addresses:
+// conflict-free; 2 LDS instead of 6 SHFL per step).  Same arithmetic, same bits.
+template <typename T, int I, int ORD, bool UM, bool EXACT, bool ROT>
+__device__ __forceinline__ void sym_strip(const typename V4<T>::type* strip, const int lane,
+										   const T (&xi)[I],
 										   const T (&yi)[I], const T (&zi)[I], const T (&mi)[I],
 										   Acc<T, I>& loc, T& ajx, T& ajy, T& ajz,
 										   const Clamp<T>& cl, int& mn, const int next_lane) {
+	const typename V4<T>::type pj = strip[lane];
 	T jx = pj.x, jy = pj.y, jz = pj.z, jm = pj.w;
 	ajx = ajy = ajz = T(0);
 #pragma unroll
@@ -131,10 +137,16 @@ __device__ __forceinline__ void sym_strip(const typename V4<T>::type pj, const T
 	for (int r = 0; r < 32; ++r) {
 		interact_sym<T, I, ORD, UM, EXACT>(jx, jy, jz, jm, xi, yi, zi, mi, loc, ajx, ajy, ajz, cl, mn);
 		// pass the j-body and its accumulator on; after 32 passes they are home again
-		jx = __shfl_sync(0xffffffffu, jx, next_lane);
-		jy = __shfl_sync(0xffffffffu, jy, next_lane);
-		jz = __shfl_sync(0xffffffffu, jz, next_lane);
-		if (!UM) jm = __shfl_sync(0xffffffffu, jm, next_lane);
+		if (ROT) {
+			const typename V4<T>::type q = strip[(lane + r + 1) & 31];
+			jx = q.x; jy = q.y; jz = q.z;
+			if (!UM) jm = q.w;
+		} else {
+			jx = __shfl_sync(0xffffffffu, jx, next_lane);
+			jy = __shfl_sync(0xffffffffu, jy, next_lane);
+			jz = __shfl_sync(0xffffffffu, jz, next_lane);
+			if (!UM) jm = __shfl_sync(0xffffffffu, jm, next_lane);
+		}
 		ajx = __shfl_sync(0xffffffffu, ajx, next_lane);
 		ajy = __shfl_sync(0xffffffffu, ajy, next_lane);
 		ajz = __shfl_sync(0xffffffffu, ajz, next_lane);
@@ -147,7 +159,7 @@ constexpr size_t force_sym_smem_bytes() {
 		   (size_t)3 * I * THREADS * sizeof(T) + STAGES * sizeof(uint64_t) + 16;
 }
 
-template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int ORD>
+template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int ORD, int ROT = 0>
 __global__ void __launch_bounds__(THREADS, MINB)
 	force_sym_kernel(const SymParams p, const Clamp<T> cl) {
 	typedef typename V4<T>::type vec4;
@@ -251,13 +263,13 @@ __global__ void __launch_bounds__(THREADS, MINB)
 				}
 			} else {
 				for (int s0 = 0; s0 < cnt; s0 += 32) {	// strips that hold a real body
-					const vec4 pj = tile[s0 + (tid & 31)];
 					T ajx, ajy, ajz;
-					sym_strip<T, I, ORD, UM != 0, false>(pj, xi, yi, zi, mi, loc, ajx, ajy, ajz, cl,
-														 mn, next_lane);
+					sym_strip<T, I, ORD, UM != 0, false, ROT != 0>(tile + s0, tid & 31, xi, yi, zi, mi,
+																   loc, ajx, ajy, ajz, cl, mn, next_lane);
 					if (__any_sync(0xffffffffu, mn <= cl.thresh))  // rare: redo the strip exactly
-						sym_strip<T, I, ORD, UM != 0, true>(pj, xi, yi, zi, mi, loc, ajx, ajy, ajz,
-															cl, mn, next_lane);
+						sym_strip<T, I, ORD, UM != 0, true, ROT != 0>(tile + s0, tid & 31, xi, yi, zi,
+																	  mi, loc, ajx, ajy, ajz, cl, mn,
+																	  next_lane);
 					const unsigned j = j_first + (unsigned)s0 + (unsigned)(tid & 31);
 					atomicAdd(gjx + j, ajx);  // result unused -> RED.ADD
 					atomicAdd(gjy + j, ajy);

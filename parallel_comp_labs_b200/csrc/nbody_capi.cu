@@ -135,29 +135,37 @@ struct SymVariant {
 	void (*launch[2])(dim3, cudaStream_t, size_t, const SymParams&, double eps2);
 	const char* name;
 };
-template <typename T, int TH, int I, int ST, int MB, int UM, int ORD>
+template <typename T, int TH, int I, int ST, int MB, int UM, int ORD, int ROT>
 void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p, double eps2) {
-	auto kern = force_sym_kernel<T, TH, I, ST, MB, UM, ORD>;
+	auto kern = force_sym_kernel<T, TH, I, ST, MB, UM, ORD, ROT>;
 	NB_LAUNCH(kern, grid, dim3(TH), smem, s, p, make_clamp<T>(eps2));
 }
-#define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD)                                                  \
+#define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT)                                             \
 	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
-				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD>,                      \
-				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD>},                     \
-				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD>, launch_force_sym<T, TH, I, ST, MB, 1, ORD>}, \
-				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD }
-// {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order}
+				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT>,                 \
+				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT>},                \
+				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT>,                              \
+				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT>},                             \
+				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT }
+// {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order, rot}
+// rot = 0: the j-body is shuffled round the warp with its accumulator; rot = 1: it is re-read
+// from the staged tile and only the accumulator is shuffled (force_sym_kernels.cuh, sym_strip).
+// New variants go at the END of a table: indices are part of the option interface.
 const SymVariant g_sym64[] = {
-	NB_SYM_VARIANT(double, 128, 4, 2, 5, 2),  // 96 registers, 20 warps/SM
-	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2),  // 128 registers, 16 warps/SM
-	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2),
-	NB_SYM_VARIANT(double, 128, 2, 2, 8, 2),
-	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2),
+	NB_SYM_VARIANT(double, 128, 4, 2, 5, 2, 0),	 // 96 registers, 20 warps/SM
+	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 0),	 // 128 registers, 16 warps/SM
+	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 0),
+	NB_SYM_VARIANT(double, 128, 2, 2, 8, 2, 0),
+	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2, 0),
+	NB_SYM_VARIANT(double, 128, 4, 2, 5, 2, 1),
+	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 1),
+	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 1),
 };
 const SymVariant g_sym32[] = {
-	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2),
-	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2),
-	NB_SYM_VARIANT(float, 128, 2, 2, 8, 2),
+	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),
+	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 0),
+	NB_SYM_VARIANT(float, 128, 2, 2, 8, 2, 0),
+	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 1),
 };
 constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
 constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);

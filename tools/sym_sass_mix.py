@@ -43,10 +43,10 @@ def hot_loop(ins):
 def main():
     rows = []
     for name, ins in sorted(functions().items()):
-        m = re.search(r"force_sym_kernelI([df])Li(\d+)ELi(\d+)ELi(\d+)ELi(\d+)ELi(\d+)ELi(\d+)E", name)
+        m = re.search(r"force_sym_kernelI([df])Li(\d+)ELi(\d+)ELi(\d+)ELi(\d+)ELi(\d+)ELi(\d+)ELi(\d+)E", name)
         if not m:
             continue
-        t, th, i, st, mb, um, order = m.group(1), *map(int, m.groups()[1:])
+        t, th, i, st, mb, um, order, rot = m.group(1), *map(int, m.groups()[1:])
         body = hot_loop(ins)
         if body is None:
             continue
@@ -59,10 +59,10 @@ def main():
         fp = sum(v for k, v in ops.items() if k in (("DFMA", "DMUL", "DADD") if t == "d" else
                                                      ("FFMA", "FMUL", "FADD", "FFMA2", "FMUL2", "FADD2")))
         other = sum(ops.values()) - fp
-        rows.append((t, i, mb, um, fp / mufu, ops.get("SHFL", 0) / mufu, other / mufu, len(body), mufu))
-    print("type I minCTA UM | FP-pipe instr/pair-eval | SHFL/pair-eval | all other/pair-eval | loop instrs (pair-evals per trip)")
+        rows.append((t, i, mb, um, rot, fp / mufu, ops.get("SHFL", 0) / mufu, other / mufu, len(body), mufu))
+    print("type I minCTA UM ROT | FP-pipe instr/pair-eval | SHFL/pair-eval | all other/pair-eval | loop instrs (pair-evals per trip)")
     for r in rows:
-        print("%s    %d  %d      %d  | %6.2f | %5.2f | %5.2f | %d (%d)" % r)
+        print("%s    %d  %d      %d  %d   | %6.2f | %5.2f | %5.2f | %d (%d)" % r)
 
 
 if __name__ == "__main__":
