@@ -160,12 +160,14 @@ const SymVariant g_sym64[] = {
 	NB_SYM_VARIANT(double, 128, 4, 2, 5, 2, 1),
 	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 1),
+	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2, 1),
 };
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),
 	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 0),
 	NB_SYM_VARIANT(float, 128, 2, 2, 8, 2, 0),
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 1),
+	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 1),
 };
 constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
 constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);

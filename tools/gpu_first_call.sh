@@ -35,7 +35,7 @@ step pytest_gpu 900 $PY -m pytest tests -m gpu -x -q
 bench_line bench_default 400 --steps 2 --warmup 3
 
 # 3. pair-symmetric kernel: variants, general masses, FP32 (no CPU leg, no energy: kernel numbers)
-for v in 0 1 2 3 4 5 6 7; do
+for v in 0 1 2 3 4 5 6 7 8; do
 	bench_line "bench_sym_v$v" 200 --pair-symmetry 1 --sym-variant $v --steps 2 --warmup 3 \
 		--no-cpu-baseline --no-energy
 done
