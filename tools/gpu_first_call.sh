@@ -39,9 +39,19 @@ for v in 0 1 2 3 4 5 6 7 8; do
 	bench_line "bench_sym_v$v" 200 --pair-symmetry 1 --sym-variant $v --steps 2 --warmup 3 \
 		--no-cpu-baseline --no-energy
 done
-bench_line bench_sym_general 200 --pair-symmetry 1 --unimass 0 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+for v in 1 5 6 7 8; do
+	bench_line "bench_sym_general_v$v" 200 --pair-symmetry 1 --sym-variant $v --unimass 0 --steps 2 --warmup 3 \
+		--no-cpu-baseline --no-energy
+done
 bench_line bench_default_general 200 --unimass 0 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
-bench_line bench_sym_fp32 200 --pair-symmetry 1 --precision 32 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+for v in 0 1 2 3 4; do
+	bench_line "bench_sym_fp32_v$v" 200 --pair-symmetry 1 --sym-variant $v --precision 32 --steps 2 --warmup 3 \
+		--no-cpu-baseline --no-energy
+done
+bench_line bench_default_fp32 200 --precision 32 --steps 2 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_default_20k 200 --bodies 20000 --dist uniform --steps 10 --warmup 3 --no-cpu-baseline --no-energy
+bench_line bench_sym_20k 200 --pair-symmetry 1 --bodies 20000 --dist uniform --steps 10 --warmup 3 --no-cpu-baseline --no-energy
+step fma_peak 120 $PY tools/fma_peak.py && cp "$OUT/fma_peak.log" "$OUT/fma_peak.json"
 bench_line bench_sym_256k 200 --pair-symmetry 1 --bodies 262144 --steps 3 --warmup 3 --no-cpu-baseline --no-energy
 bench_line bench_default_256k 200 --bodies 262144 --steps 3 --warmup 3 --no-cpu-baseline --no-energy
 
@@ -59,4 +69,16 @@ if [ -s "$OUT/bench_sym_v0.json" ]; then
 		-k regex:force_sym_kernel -c 1 -o "$OUT/force_sym_kernel_131072" -f \
 		$PY tools/rhs_once.py --bodies 131072 --pair-symmetry 1
 fi
+for cfg in "fp32 --precision 32" "general --unimass 0"; do
+	set -- $cfg; nm=$1; shift
+	step ncu_full_default_$nm 600 ncu --set full --clock-control none --import-source on \
+		-k regex:force_kernel -c 1 -o "$OUT/force_kernel_131072_$nm" -f \
+		$PY tools/rhs_once.py --bodies 131072 "$@"
+	step ncu_full_sym_$nm 600 ncu --set full --clock-control none --import-source on \
+		-k regex:force_sym_kernel -c 1 -o "$OUT/force_sym_kernel_131072_$nm" -f \
+		$PY tools/rhs_once.py --bodies 131072 --pair-symmetry 1 "$@"
+done
+# 5. compute-sanitizer (memcheck / racecheck / synccheck) over every kernel at small N
+SAN_TIMEOUT=420 bash tools/sanitize.sh > "$OUT/sanitize.log" 2>&1
+cat gpurun_out/sanitize/summary.txt >> "$OUT/summary.txt"
 cat "$OUT/summary.txt"
