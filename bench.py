@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--sym-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
+    ap.add_argument("--no-parity", action="store_true",
+                    help="skip the post-run check of owned RHS rows against the oracle")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
 
@@ -174,7 +176,7 @@ def run_reference(args):
         "ms_per_step": stages * n * n / (value * 1e9) * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": workload_config(args, tau, eps, None),
+        "config": workload_config(args, tau, eps, "n/a"),
         "cpu_baseline": dict(info, value=value),
         "e2e": {"value": value, "unit": "G interactions/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
@@ -201,6 +203,39 @@ def workload_config(args, tau, eps, variant):
                             f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
                             f"per RK stage overlapped with the local-tile force launch"),
             "kernel_variant": variant}
+
+
+# ---------------------------------------------------------------- post-run parity (checker only)
+def parity_block(ctx, bodies, eps, precision, rows_per_run=32, runs=4):
+    """After the timed region: this rank evaluates one RHS of the bench's initial state through
+    the library and checks `runs` x `rows_per_run` of ITS OWNED rows against the oracle (the
+    reference's begin,end API, struct_ode_system.hpp:53-57: rows [b,e) against all N bodies).
+    The oracle is used here as the checker only; nothing it computes is timed or shipped.
+    Returns (rows, norm_relative_error, worst_per_row_error)."""
+    from oracle import Oracle
+    o = Oracle()
+    n = bodies.shape[0]
+    dtype = np.float64 if precision == 64 else np.float32
+    ctx.upload_aos(np.ascontiguousarray(bodies, dtype=dtype))
+    got = ctx.rhs().astype(np.float64)
+    b, e = ctx.owned_range()
+    own = e - b
+    if own <= 0:
+        return 0, 0.0, 0.0
+    rows_per_run = min(rows_per_run, own)
+    starts = sorted({b + int(k * (own - rows_per_run) / max(runs - 1, 1)) for k in range(runs)})
+    worst_norm = worst_row = 0.0
+    ref64 = np.ascontiguousarray(bodies.astype(dtype), dtype=np.float64)  # the values the GPU holds
+    for s0 in starts:
+        want = o.rhs(ref64, s0, s0 + rows_per_run, eps=eps, threads=2)[s0:s0 + rows_per_run, 4:7]
+        g = got[s0:s0 + rows_per_run]
+        worst_norm = max(worst_norm, float(np.abs(g - want).max() / np.abs(want).max()))
+        worst_row = max(worst_row, float((np.abs(g - want).max(axis=1)
+                                          / np.maximum(np.abs(want).max(axis=1), 1e-300)).max()))
+    return len(starts) * rows_per_run, worst_norm, worst_row
+
+
+PARITY_TOL = {64: (1e-12, 1e-10), 32: (1e-4, 2e-3)}     # (norm-relative, per-row) -- tests/ hold the same
 
 
 # ---------------------------------------------------------------- this framework
@@ -320,6 +355,17 @@ def run_b200(args):
             e2e_ms.append(max_over_ranks(dt))
     e2e_value = stages * float(n) * float(n) * len(e2e_ms) / (sum(e2e_ms) * 1e-3) / 1e9
     bytes_io = n * 7 * np.dtype(dtype).itemsize
+    # ---- parity of THIS run's configuration (every rank checks rows it owns; not timed) -------
+    parity = None
+    if not args.no_parity:
+        prow, pnorm, pper = parity_block(ctx, bodies, eps, args.precision)
+        tol_norm, tol_row = PARITY_TOL[args.precision]
+        parity = {"rows": int(sum_over_ranks(float(prow))), "rows_per_rank": int(prow),
+                  "rhs_rel_err": max_over_ranks(pnorm), "per_row_max": max_over_ranks(pper),
+                  "tolerance": {"rhs_rel_err": tol_norm, "per_row": tol_row},
+                  "checker": "oracle/nbody_oracle.c (bit-exact restatement of lab_4 N_body_func), "
+                             "rows [b,e) of each rank's owned block against all N bodies"}
+        parity["ok"] = bool(parity["rhs_rel_err"] < tol_norm and parity["per_row_max"] < tol_row)
     total_launches = int(sum_over_ranks(float(launches)))
     sum_pairs = sum_over_ranks(float(pair_evals))
 
@@ -368,6 +414,7 @@ def run_b200(args):
             "pct_of_fp_peak_whole_job": 100.0 * FLOPS_PER_INTERACTION * value * 1e9 / 1e12
                                         / (peak * world),
             "energy_drift": (abs(e1 - e0) / abs(e0)) if e0 else None,
+            "parity": parity,
         }
     ctx.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -382,6 +429,8 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        raise SystemExit(f"PARITY FAILED: {parity}")
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed

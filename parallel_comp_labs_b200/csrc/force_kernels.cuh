@@ -214,6 +214,9 @@ struct ForceParams {
 	// exchange (nbody_p2p_connect) blk[r] for r != rank points INTO RANK r's HBM over NVLink and
 	// the bulk-async copies fetch the remote tiles directly: no separate collective.
 	const void* blk[8];
+	const void* own;	   // this rank's block (i-body source)
+	unsigned contiguous;   // 1: all blocks are consecutive in ONE array starting at blk[0] (NCCL
+						   //    exchange, any number of ranks); 0: per-rank table (peer-pull, <= 8)
 	unsigned jt_per_rank;  // j-tiles per block
 	unsigned rank;
 	void* apart;		   // V4[n_slices_total][own_pad] raw partial sums (w unused)
@@ -236,6 +239,7 @@ template <typename T> struct Tile {
 // global address of j-tile `jt` (absolute tile index): block of its owner + offset inside it
 template <typename vec4, int TJ>
 __device__ __forceinline__ const vec4* tile_src(const ForceParams& p, unsigned jt) {
+	if (p.contiguous) return reinterpret_cast<const vec4*>(p.blk[0]) + (size_t)jt * TJ;
 	const unsigned r = jt / p.jt_per_rank;
 	return reinterpret_cast<const vec4*>(p.blk[r]) + (size_t)(jt - r * p.jt_per_rank) * TJ;
 }
@@ -254,7 +258,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	volatile unsigned* next_unit_s = reinterpret_cast<volatile unsigned*>(full + STAGES);
 
 	const int tid = threadIdx.x;
-	const vec4* __restrict__ own = reinterpret_cast<const vec4*>(p.blk[p.rank]);
+	const vec4* __restrict__ own = reinterpret_cast<const vec4*>(p.own);
 	vec4* __restrict__ apart = reinterpret_cast<vec4*>(p.apart);
 
 	if (tid == 0) {

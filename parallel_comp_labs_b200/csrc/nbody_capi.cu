@@ -454,12 +454,16 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 	const Variant& v = variant_of(ctx);
 	ForceParams p;
 	const size_t block_bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
+	// NCCL exchange: every block lives in this GPU's own array -> one base pointer, any number of
+	// ranks.  Peer-pull exchange (<= 8 ranks): blk[r] points into rank r's HBM.
+	p.contiguous = !(remote && ctx->p2p);
 	for (int r = 0; r < 8; ++r) {
 		const char* base = (const char*)buf_ptr(ctx, buf);
 		if (remote && ctx->p2p && r < ctx->world && r != ctx->rank)
 			base = (const char*)(buf == BUF_Y ? ctx->peerY[r] : ctx->peerP[buf == BUF_P ? 1 : 0][r]);
 		p.blk[r] = r < ctx->world ? base + (size_t)r * block_bytes : nullptr;
 	}
+	p.own = (const char*)buf_ptr(ctx, buf) + (size_t)ctx->rank * block_bytes;
 	p.jt_per_rank = lp.jt_per_rank;
 	p.rank = (unsigned)ctx->rank;
 	p.apart = ctx->apart;
@@ -755,6 +759,11 @@ StepCoef builtin_coef(const nbody_ctx* ctx, int scheme, double tau) {
 int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, const StepCoef& k) {
 	int rc;
 	const int ns = k.ns;
+	// peer-pull exchange: a 1-stage scheme overwrites this rank's block of Y right after its own
+	// force launch, while peers may still be pulling it (no later epoch covers that read)
+	if (ctx->p2p && ns < 2)
+		return fail(ctx, NBODY_ERR_STATE, "1-stage schemes need the NCCL exchange (peer-pull has no "
+										  "acknowledgement before the state is overwritten)");
 	const double* c = k.c;
 	const double* b = k.b;
 	const double fs = k.fs;
@@ -784,6 +793,9 @@ int enqueue_step(nbody_ctx* ctx, const LaunchPlan& lp, const StepCoef& k) {
 // one step of a general explicit RK scheme (all k_j resident), enqueued on sc (+ sm)
 int enqueue_step_general(nbody_ctx* ctx, const LaunchPlan& lp, const GenCoef& k) {
 	int rc;
+	if (ctx->p2p && k.ns < 2)
+		return fail(ctx, NBODY_ERR_STATE, "1-stage schemes need the NCCL exchange (peer-pull has no "
+										  "acknowledgement before the state is overwritten)");
 	for (int s = 0; s < k.ns; ++s) {
 		const StageBuf buf = stage_buf(ctx, s);
 		const GatherMode mode = s > 0 ? GATHER_NOW : (ctx->y_pending ? GATHER_PENDING_Y : GATHER_NONE);
@@ -1125,6 +1137,9 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 static int upload_common(nbody_ctx* ctx) {
 	ctx->undo_valid = false;
 	ctx->k0_slot = -1;
+	// a captured step bakes kernel parameters in by value (the uniform mass among them): never
+	// replay a graph across an upload
+	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 	if (ctx->P2)  // pad rows and masses of the second stage buffer
 		CK(cudaMemcpy(ctx->P2, ctx->P, (size_t)ctx->n_pad * 4 * ctx->esz, cudaMemcpyDeviceToDevice));
 	if (ctx->p2p) {	 // peers read this rank's block of Y from here on: publish it

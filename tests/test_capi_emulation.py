@@ -235,7 +235,8 @@ def _run_ranks(world, bodies, eps, tau, steps, **options):
 
 
 @pytest.mark.parametrize("world,opts", [(2, {}), (3, {}), (2, {"pair_symmetry": 1}),
-                                        (3, {"pair_symmetry": 1, "slices": 2})])
+                                        (3, {"pair_symmetry": 1, "slices": 2}),
+                                        (9, {})])   # > 8 ranks: one base pointer, no per-rank table
 def test_emulated_abi_several_ranks(oracle, world, opts):
     """world > 1 through the whole ABI: block partition, all-gather of the stage positions (and the
     eager gather of y_{n+1}), for the pair-symmetric kernel the reduce-scatter of the j-side sums,
@@ -435,3 +436,20 @@ def test_emulated_cxx_driver_reference_run_and_schemes(emulated_driver, golden, 
     assert abs(rows_ad[-1, 0] - 2.0) < 1e-12 and '"rejected"' in out
     exact = np.array([np.interp(rows_ad[-1, 0], golden["traj1"][:, 0], golden["traj1"][:, k]) for k in (1, 2, 3)])
     assert np.abs(rows_ad[-1, 1:4] - exact).max() < 2e-5
+
+
+def test_emulated_graph_is_not_replayed_across_uploads(oracle):
+    """A captured step holds the uniform mass by value: re-uploading the same bodies with a
+    DIFFERENT equal mass on one context must not replay the old graph."""
+    n = 64
+    b = generators.uniform_bodies(n, seed=2)
+    with capi.Context(n, 64) as ctx:
+        ctx.set_option("use_graph", 1)
+        for mass in (1e9, 3e9):
+            b[:, 0] = mass
+            want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, max_steps=3, rows=False)
+            ctx.upload_aos(b)
+            ctx.step(capi.NBODY_RK4, 0.1, 3, sync=True)
+            got = ctx.download_aos()
+            assert ctx.timing().uniform_mass == 1
+            check_state(got, want, b, 1e-10)

@@ -425,3 +425,18 @@ def test_python_host_mirror_writes_reference_files(golden, tmp_path):
     tcsv = open(tmp_path / "output_4Body_test_0.100000_np_1.csv").read().splitlines()
     assert tcsv[0] == "size;t_start;t_finish;tau;time_steps;num_procs;time_taken;avg_time_for_step"
     assert tcsv[1].startswith("4;0;20;0.1;200;1;")
+
+
+def test_graph_is_not_replayed_across_uploads(oracle):
+    """Re-upload with a different equal mass on one context, stepping through the CUDA-graph path:
+    the captured step bakes the uniform mass into K2's parameters, so the graph must be dropped."""
+    n = 64
+    b = generators.uniform_bodies(n, seed=2)
+    with capi.Context(n, 64) as ctx:
+        ctx.set_option("use_graph", 1)
+        for mass in (1e9, 3e9):
+            b[:, 0] = mass
+            want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, max_steps=3, rows=False)
+            ctx.upload_aos(b)
+            ctx.step(capi.NBODY_RK4, 0.1, 3, sync=True)
+            check_state(ctx.download_aos().astype(np.float64), want, b, TOL64_TRAJ, steps=3)

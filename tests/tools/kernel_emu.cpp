@@ -74,6 +74,8 @@ int rhs_impl(unsigned n, const double* bodies, double G, double eps, int sym, in
 		ForceParams p;
 		memset(&p, 0, sizeof(p));
 		p.blk[0] = Y.data();
+		p.own = Y.data();
+		p.contiguous = 1;
 		p.jt_per_rank = jt_total;
 		p.rank = 0;
 		p.own0 = 0;
