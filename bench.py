@@ -48,12 +48,16 @@ def parse():
     ap.add_argument("--unimass", type=int, default=-1, help="-1 auto-detect equal masses, 0 off")
     ap.add_argument("--p2p", type=int, default=0,
                     help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
-    ap.add_argument("--pair-symmetry", type=int, default=0,
-                    help="1: evaluate each pair of distinct bodies once and credit both "
-                         "(opt-in; the default evaluates every ordered pair as the reference does)")
+    ap.add_argument("--pair-symmetry", type=int, default=-1,
+                    help="-1: the library's automatic choice (pair-symmetric kernel for N >= 49152); "
+                         "1: evaluate each pair of distinct bodies once and credit both; "
+                         "0: the one-sided kernel (every ordered pair, as the reference does; "
+                         "bit-reproducible)")
     ap.add_argument("--sym-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the 2-step general-mass (unimass=0) figure")
     ap.add_argument("--no-parity", action="store_true",
                     help="skip the post-run check of owned RHS rows against the oracle")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -196,10 +200,10 @@ def workload_config(args, tau, eps, variant):
             "parallelism": (f"i-rows over {args.gpus} GPU(s), peer-pull exchange: remote j-tiles "
                             f"fetched from the peers' HBM by the force kernel's bulk-async copies"
                             if getattr(args, "p2p", 0) and args.gpus > 1 else
-                            f"pair-symmetric kernel (opt-in): the blocks of one global schedule split "
+                            f"pair-symmetric kernel: the blocks of one global schedule split "
                             f"over {args.gpus} GPU(s); per RK stage an NCCL all-gather of the packed "
-                            f"positions (waited for) and a reduce-scatter of the j-side sums"
-                            if getattr(args, "pair_symmetry", 0) else
+                            f"positions (waited for) and a reduce-scatter of the acceleration sums"
+                            if getattr(args, "sym_in_use", False) else
                             f"i-rows over {args.gpus} GPU(s), NCCL all-gather of packed positions "
                             f"per RK stage overlapped with the local-tile force launch"),
             "kernel_variant": variant}
@@ -297,9 +301,8 @@ def run_b200(args):
     ctx.set_params(6.67e-11, eps)
     ctx.set_option("variant", args.variant)
     ctx.set_option("unimass", args.unimass)
-    if args.pair_symmetry:
-        ctx.set_option("pair_symmetry", 1)
-        ctx.set_option("sym_variant", args.sym_variant)
+    ctx.set_option("pair_symmetry", args.pair_symmetry)
+    ctx.set_option("sym_variant", args.sym_variant)
     host_in = capi.PinnedArray((n, 7), dtype)
     host_out = capi.PinnedArray((n, 7), dtype)
     host_in.array[:] = bodies.astype(dtype)
@@ -343,18 +346,31 @@ def run_b200(args):
     force_share = max_over_ranks(force_ms) / total_ms
 
     # ---- end-to-end through the public API with pinned host buffers --------------------------
+    # One rank: the whole state goes up and comes back (nbody_upload_aos / nbody_download_aos).
+    # Several ranks: each rank moves only the rows it owns through PCIe (nbody_upload_aos_owned /
+    # nbody_download_aos_owned, as an MPI rank of lab_4 owns rows [offsets[id], +counts[id]));
+    # the full position array is assembled by an all-gather over NVLink.  Bytes per step are the
+    # same in total; they are the sum over ranks of what each rank copies.
     e2e_ms = []
+    ob, oe = ctx.owned_range()
+    own_in = host_in.array[ob:oe]
+    own_out = host_out.array[ob:oe]
     for k in range(1 + args.steps):        # first pass untimed
         barrier()
         t0 = time.perf_counter()
-        ctx.upload_aos(host_in.array)      # H2D of the step's input state
-        ctx.step(scheme, tau, 1)
-        ctx.download_aos(host_out.array)   # D2H of the step's result (collective gather of v)
+        if world == 1 or args.p2p:
+            ctx.upload_aos(host_in.array)      # H2D of the step's input state
+            ctx.step(scheme, tau, 1)
+            ctx.download_aos(host_out.array)   # D2H of the step's result
+        else:
+            ctx.upload_aos_owned(own_in)
+            ctx.step(scheme, tau, 1)
+            ctx.download_aos_owned(own_out)
         dt = (time.perf_counter() - t0) * 1e3
         if k:
             e2e_ms.append(max_over_ranks(dt))
     e2e_value = stages * float(n) * float(n) * len(e2e_ms) / (sum(e2e_ms) * 1e-3) / 1e9
-    bytes_io = n * 7 * np.dtype(dtype).itemsize
+    bytes_io = n * 7 * np.dtype(dtype).itemsize * (world if (world > 1 and args.p2p) else 1)
     # ---- parity of THIS run's configuration (every rank checks rows it owns; not timed) -------
     parity = None
     if not args.no_parity:
@@ -366,9 +382,41 @@ def run_b200(args):
                   "checker": "oracle/nbody_oracle.c (bit-exact restatement of lab_4 N_body_func), "
                              "rows [b,e) of each rank's owned block against all N bodies"}
         parity["ok"] = bool(parity["rhs_rel_err"] < tol_norm and parity["per_row_max"] < tol_row)
+    # ---- secondary figure: the same workload with the uniform-mass specialisation OFF ----------
+    # (the Plummer bodies have equal masses, which the library detects and factors out of the
+    # pair sum; inputs with distinct masses -- the reference's own rand_bodies.txt -- take the
+    # general-mass kernels: one more FP64 instruction per pair / two more per pair evaluation)
+    secondary = None
+    if not args.no_secondary and tm.uniform_mass and args.unimass != 0:
+        uid2 = None
+        if world > 1:
+            box = [capi.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            uid2 = box[0]
+        with capi.Context(n, args.precision, local, rank, world, uid2) as c2:
+            c2.set_params(6.67e-11, eps)
+            c2.set_option("unimass", 0)
+            c2.set_option("pair_symmetry", args.pair_symmetry)
+            c2.upload_aos(host_in.array)
+            c2.step(scheme, tau, 1)
+            c2.sync()
+            ms2 = []
+            for _ in range(2):
+                barrier()
+                c2.step(scheme, tau, 1)
+                c2.sync()
+                ms2.append(max_over_ranks(c2.timing().last_call_ms))
+            t2 = c2.timing()
+            secondary = {"general_masses": {
+                "value": stages * float(n) * float(n) * 2 / (sum(ms2) * 1e-3) / 1e9,
+                "unit": "G interactions/s", "steps": 2, "warmup": 1,
+                "uniform_mass_factored_out": bool(t2.uniform_mass),
+                "pair_symmetry": bool(t2.pair_symmetry),
+                "note": "same bodies, option unimass=0: the kernels any input with distinct masses gets"}}
     total_launches = int(sum_over_ranks(float(launches)))
     sum_pairs = sum_over_ranks(float(pair_evals))
 
+    args.sym_in_use = bool(tm.pair_symmetry)
     line = None
     if rank == 0:
         variant_name = {"variant": int(tm.variant), "uniform_mass_factored_out": bool(tm.uniform_mass),
@@ -379,7 +427,7 @@ def run_b200(args):
             # every pair evaluation serves two interactions: 18 (20 with general masses) FP64
             # instructions per evaluation; `value` and roofline.achieved count DELIVERED
             # interactions (the metric's definition), roofline.evaluated_* what was computed
-            variant_name.update({"pair_symmetry": True, "sym_variant": max(args.sym_variant, 0),
+            variant_name.update({"pair_symmetry": True, "sym_variant": int(tm.sym_variant),
                                  "fp64_instr_per_pair": None,
                                  "fp64_instr_per_pair_evaluation":
                                      (18 if tm.uniform_mass else 20) if args.precision == 64 else None})
@@ -415,6 +463,7 @@ def run_b200(args):
                                         / (peak * world),
             "energy_drift": (abs(e1 - e0) / abs(e0)) if e0 else None,
             "parity": parity,
+            "secondary": secondary,
         }
     ctx.close()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -54,7 +54,7 @@ typedef struct nbody_timing {
 									== interactions for the default kernels, about half of it with
 									option "pair_symmetry" (each evaluation serves both bodies) */
 	uint32_t pair_symmetry;		 /* 1 if the pair-symmetric kernels are in use */
-	uint32_t reserved_;
+	uint32_t sym_variant;		 /* pair-symmetric kernel variant index in use (0 if not in use) */
 } nbody_timing;
 
 /* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
@@ -98,19 +98,23 @@ int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 
 /* G and eps captured by the RHS lambda (lab_4 .../struct_ode_system.hpp:34-36,53;
  * lab_5 N_body.cu:22,30).  Defaults 6.67e-11 and 1e-6. */
-int nbody_set_params(nbody_ctx* ctx, double G, double eps);
+int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab_5 #defines G (N_body.cu:30) */
 
 /* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
  * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (-1 = auto: CUDA-graph replay of a step when n <= 16384 on one GPU; 0/1),
  * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
  * sum, the default; 0 = never; set before the upload),
- * "pair_symmetry" (0 = default: every ordered pair is evaluated, as the reference does; 1 =
- * every pair of distinct bodies is evaluated once and credited to both bodies (Newton's third
- * law) -- same per-pair bits, about half the arithmetic; j-side sums are collected with
- * floating-point atomics, so results are reproducible to rounding only; on several GPUs the
- * ranks split the blocks of one global schedule and the j-side sums are reduce-scattered
- * (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose block divides the
- * per-rank block of nbody_partition, a forced variant that does not is NBODY_ERR_STATE)),
+ * "pair_symmetry" (which force kernel runs.  0 = every ordered pair is evaluated separately, as
+ * the reference does: the one-sided kernel, BIT-REPRODUCIBLE run to run (fixed-order sums);
+ * 1 = every pair of distinct bodies is evaluated once and credited to both bodies (Newton's third
+ * law) -- same per-pair bits, about half the arithmetic, 1.5x the throughput; both sides are
+ * summed with floating-point atomics, so results are reproducible to ROUNDING only (same
+ * tolerances against the reference); -1 = automatic, the default: the pair-symmetric kernel for
+ * n >= 49152 unless the peer-pull exchange is connected, the one-sided kernel below that.
+ * On several GPUs the ranks split the blocks of one global schedule and the sums are
+ * reduce-scattered (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose
+ * block divides the per-rank block of nbody_partition, a forced variant that does not is
+ * NBODY_ERR_STATE).  nbody_timing.pair_symmetry reports which kernel ran),
  * "sym_variant" (kernel variant id of that mode, -1 = default). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 
@@ -123,6 +127,12 @@ int nbody_owned_range(const nbody_ctx* ctx, size_t* begin, size_t* end);
  * (N_body.cu:279-288).  Host pointers are borrowed for the call only. */
 int nbody_upload_aos(nbody_ctx* ctx, const void* bodies);
 int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* v4);
+/* Scalable variant for several GPUs: every rank passes ONLY the rows it owns (own_real x Body<T>,
+ * rows [begin,end) of nbody_owned_range -- &sys.traj_init[offsets[id]] in lab_4's terms,
+ * class_Solver_N_body.hpp:119-130); the full position array is assembled on the devices by one
+ * all-gather over NVLink (what MPI_Allgatherv of `sol` does at ode_RK2_MPI.hpp:91) instead of
+ * every rank pushing all n bodies through PCIe.  Collective over the world; NCCL exchange only. */
+int nbody_upload_aos_owned(nbody_ctx* ctx, const void* owned_bodies);
 
 /* Test hook == sys.N_body_func(traj, diff, begin, end) with [begin,end) = owned rows
  * (lab_4 .../struct_ode_system.hpp:27-30,53-76; lab_5 calc_acceleration N_body.cu:134-195).
@@ -187,6 +197,8 @@ int nbody_snapshot_release(nbody_ctx* ctx, uint64_t ticket);
  * only visible through the CSV; needed for parity on velocities).  Collective when
  * world > 1 (velocities are owner-local and are gathered here): all ranks must call it. */
 int nbody_download_aos(nbody_ctx* ctx, void* bodies);
+/* The owned rows only (own_real x Body<T>): not a collective, nothing but this rank's block moves. */
+int nbody_download_aos_owned(nbody_ctx* ctx, void* owned_bodies);
 
 /* Kinetic and potential energy of the current state, potential consistent with the
  * clamp force.  Not in the reference.  Collective when world > 1. */
@@ -211,6 +223,10 @@ int nbody_measure_fma_peak(int device, int precision, double ms_target, double* 
 
 const char* nbody_last_error(const nbody_ctx* ctx);
 const char* nbody_version(void);
+/* Number of sm_100 devices this process can use (0 if none or no driver): lets a multi-GPU host
+ * validate `--gpus` BEFORE it spawns ranks that would otherwise wait for each other forever in
+ * the communicator set-up (the reference has no counterpart: mpirun sizes the world). */
+int nbody_device_count(void);
 
 #ifdef __cplusplus
 }

@@ -28,6 +28,7 @@ typedef std::ptrdiff_t MPI_Aint;
 #define MPI_COMM_WORLD 0
 #define MPI_DATATYPE_NULL 0
 #define MPI_DOUBLE 1
+#define MPI_BYTE (-1)
 #define MPI_SUCCESS 0
 #define MPI_IN_PLACE ((void*)-1)
 
@@ -153,6 +154,22 @@ inline int MPI_Type_get_extent(MPI_Datatype t, MPI_Aint* lb, MPI_Aint* extent) {
 }
 inline int MPI_Type_commit(MPI_Datatype*) { return MPI_SUCCESS; }
 inline int MPI_Type_free(MPI_Datatype*) { return MPI_SUCCESS; }
+
+/* Not used by the reference's current sources (only by its stale binary); used by
+ * the INTEGRATION.md patch to hand the NCCL unique id to every rank.  MPI_BYTE only. */
+inline int MPI_Bcast(void* buf, int count, MPI_Datatype /*MPI_BYTE*/, int root, MPI_Comm) {
+	mpi_shim::World& w = mpi_shim::world();
+	if (w.size == 1) return MPI_SUCCESS;
+	const int me = mpi_shim::my_rank();
+	{
+		std::lock_guard<std::mutex> lk(w.mu);
+		w.bufs[me] = buf;
+	}
+	mpi_shim::barrier();
+	if (me != root) std::memcpy(buf, w.bufs[root], (std::size_t)count);
+	mpi_shim::barrier();
+	return MPI_SUCCESS;
+}
 
 /* Only the form the reference uses: sendbuf == MPI_IN_PLACE. */
 inline int MPI_Allgatherv(const void* /*MPI_IN_PLACE*/, int, MPI_Datatype, void* recvbuf,

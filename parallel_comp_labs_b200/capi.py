@@ -33,7 +33,7 @@ class Timing(C.Structure):
                 ("interactions", C.c_uint64), ("steps_done", C.c_uint64),
                 ("uniform_mass", C.c_uint32), ("variant", C.c_uint32),
                 ("pair_evaluations", C.c_uint64), ("pair_symmetry", C.c_uint32),
-                ("reserved_", C.c_uint32)]
+                ("sym_variant", C.c_uint32)]
 
 
 def build_library(quiet: bool = True) -> None:
@@ -64,6 +64,7 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_last_error.restype = C.c_char_p
     L.nbody_last_error.argtypes = [vp]
     L.nbody_nccl_unique_id.argtypes = [vp]
+    L.nbody_device_count.restype = C.c_int
     L.nbody_create.argtypes = [C.POINTER(vp), sz, C.c_int, C.c_int, C.c_int, C.c_int, vp]
     L.nbody_destroy.argtypes = [vp]
     L.nbody_destroy.restype = None
@@ -76,6 +77,8 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_owned_range.argtypes = [vp, C.POINTER(sz), C.POINTER(sz)]
     L.nbody_upload_aos.argtypes = [vp, vp]
     L.nbody_upload_soa.argtypes = [vp, vp, vp, vp]
+    L.nbody_upload_aos_owned.argtypes = [vp, vp]
+    L.nbody_download_aos_owned.argtypes = [vp, vp]
     L.nbody_rhs.argtypes = [vp, vp]
     L.nbody_step.argtypes = [vp, C.c_int, C.c_double, C.c_long]
     L.nbody_step_tableau.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
@@ -213,6 +216,21 @@ class Context:
         b = np.ascontiguousarray(bodies, dtype=self.dtype)
         assert b.shape == (self.n, 7), b.shape
         self._ck(self.L.nbody_upload_aos(self.h, b.ctypes.data))
+
+    def upload_aos_owned(self, owned):
+        """Collective: this rank's rows [owned_range()) only; the rest arrives by all-gather."""
+        b, e = self.owned_range()
+        o = np.ascontiguousarray(owned, dtype=self.dtype)
+        assert o.shape == (e - b, 7), (o.shape, b, e)
+        self._ck(self.L.nbody_upload_aos_owned(self.h, o.ctypes.data if o.size else None))
+
+    def download_aos_owned(self, out=None):
+        b, e = self.owned_range()
+        if out is None:
+            out = np.empty((e - b, 7), dtype=self.dtype)
+        assert out.shape == (e - b, 7) and out.flags.c_contiguous
+        self._ck(self.L.nbody_download_aos_owned(self.h, out.ctypes.data if out.size else None))
+        return out
 
     def upload_soa(self, m, r4, v4):
         m = np.ascontiguousarray(m, dtype=self.dtype)

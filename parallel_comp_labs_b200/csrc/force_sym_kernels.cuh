@@ -67,8 +67,9 @@ inline void mbar_wait_guarded(uint64_t* bar, uint32_t parity) { mbar_wait(bar, p
 
 struct SymParams {
 	const void* pos;	 // V4[(jt_total + tpb) * TJ] positions {x,y,z,m}; rows >= n_pad unspecified
-	void* apart;		 // V4[n_slices][nb_own * BLOCK] i-side partial sums of the owned blocks
-	void* aj;			 // T[3][rows_pad] j-side sums (global row index), zeroed before the launch
+	void* aj;			 // T[3][rows_pad] acceleration sums (global row index), zeroed before the launch:
+						 //   BOTH sides of every pair are added here with RED.ADD -- the i-side sum of a
+						 //   unit once at its end, the j-side sum of a strip once per warp and strip
 	unsigned rows_pad;	 // nb * BLOCK, BLOCK = THREADS * I
 	unsigned nb;		 // blocks of the whole problem
 	unsigned block0;	 // first block this GPU owns (multi-GPU: the ranks split the blocks, every
@@ -179,7 +180,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	const int tid = threadIdx.x;
 	const int next_lane = (tid + 1) & 31;
 	const vec4* __restrict__ pos = reinterpret_cast<const vec4*>(p.pos);
-	vec4* __restrict__ apart = reinterpret_cast<vec4*>(p.apart);
 	T* __restrict__ gjx = reinterpret_cast<T*>(p.aj);
 	T* __restrict__ gjy = gjx + p.rows_pad;
 	T* __restrict__ gjz = gjy + p.rows_pad;
@@ -193,7 +193,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
 
 	uint32_t ring = 0;	// tiles consumed so far by this CTA
 	const unsigned n_units = p.nb_own * p.n_slices;
-	const size_t apart_stride = (size_t)p.nb_own * BLOCK;
 
 	unsigned unit = blockIdx.x;
 	while (unit < n_units) {
@@ -292,15 +291,16 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			}
 		}
 
-		vec4* out = apart + (size_t)slice * apart_stride + (size_t)a_loc * BLOCK + tid;
+		// i-side sums of this unit: into the same global rows the j-side reactions go to (the
+		// summation order over units and strips is scheduling-dependent either way, so the slices
+		// of a block's walk need no partial-sum rows of their own and can be as fine as the tail
+		// of the launch wants them)
 #pragma unroll
 		for (int k = 0; k < I; ++k) {
-			vec4 o;
-			o.x = accm[(0 * I + k) * THREADS + tid];
-			o.y = accm[(1 * I + k) * THREADS + tid];
-			o.z = accm[(2 * I + k) * THREADS + tid];
-			o.w = T(0);
-			out[k * THREADS] = o;
+			const unsigned row = row0 + k * THREADS;	 // < rows_pad = nb * BLOCK
+			atomicAdd(gjx + row, accm[(0 * I + k) * THREADS + tid]);  // result unused -> RED.ADD
+			atomicAdd(gjy + row, accm[(1 * I + k) * THREADS + tid]);
+			atomicAdd(gjz + row, accm[(2 * I + k) * THREADS + tid]);
 		}
 		if (tid == 0) *next_unit_s = next_ticket;
 		__syncthreads();

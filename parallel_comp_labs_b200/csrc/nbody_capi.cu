@@ -36,7 +36,7 @@ namespace {
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2 };
+enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2, NCCL_MIN = 3 };
 struct NcclApi {
 	void* lib = nullptr;
 	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
@@ -175,7 +175,8 @@ constexpr unsigned SYM_EXTRA_TILES = 4;	 // rows allocated past n_pad: phantom t
 constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
 constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
 constexpr unsigned PAD_UNIT = 256;	 // == TJ: per-rank blocks are whole j-tiles
-constexpr unsigned MAX_SLICES = 64;
+constexpr unsigned MAX_SLICES = 64;		  // default kernel: one partial-sum row per slice
+constexpr unsigned MAX_SYM_SLICES = 4096;  // pair-symmetric kernel: slices cost no memory
 }  // namespace
 
 struct nbody_ctx {
@@ -191,7 +192,7 @@ struct nbody_ctx {
 	size_t apart_bytes = 0;
 	void* aj = nullptr;		 // T[3][aj_rows] j-side sums of the pair-symmetric kernel
 	unsigned aj_rows = 0;
-	long opt_pair_symmetry = 0, opt_sym_variant = -1;
+	long opt_pair_symmetry = -1, opt_sym_variant = -1;
 	// general tableaux (nbody_step_rk / nbody_step_embedded): resident stage derivatives, the
 	// norms of the last embedded step, and the state before it (nbody_step_undo)
 	void *kr = nullptr, *kv = nullptr;
@@ -276,22 +277,41 @@ const Variant& variant_of(const nbody_ctx* c) {
 	return tab[v];
 }
 
+// Pair-symmetric variant in use.  An explicit "sym_variant" wins; otherwise the first entry of a
+// preference list (measured on B200, profiles/r02_sym_sweep.md: N = 1M, G interactions/s) whose
+// block (threads * i-bodies) divides the per-rank block of the partition -- on several GPUs the
+// ranks must own whole blocks; the 256-row builds always fit.
+//   FP64 equal masses:   8 (I=8, re-read j) 1710 | 7 (I=6) 1708 | 5 (I=4, 5 CTAs/SM) 1696 | 3 (I=2) 1484
+//   FP64 general masses: 7 (I=6) 1522 | 5 1506 | 8 1493
+//   FP32:                1 (I=8, shuffled j) 3704 | 4 3437 | 0 3374 | 3 3254 | 2 (I=2) 3026
 const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
 	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
 	long v = c->opt_sym_variant;
 	if (v >= 0 && v < nv) return tab[v];
-	// auto: the first variant whose block (threads * i-bodies) divides the per-rank block of the
-	// partition -- on several GPUs the ranks must own whole blocks; 256-row blocks always fit
-	if (c->world > 1 && c->own_pad % (unsigned)(tab[0].threads * tab[0].ipt) != 0) {
-		for (int k = 0; k < nv; ++k)
-			if (c->own_pad % (unsigned)(tab[k].threads * tab[k].ipt) == 0) return tab[k];
+	static const int pref64_um[] = {8, 5, 3}, pref64_gen1[] = {7, 5, 3}, pref64_gen[] = {5, 8, 3},
+					 pref32[] = {1, 3, 2};
+	const int* pref = c->prec == 32 ? pref32
+					  : c->unimass	? pref64_um
+					  : c->world == 1 ? pref64_gen1
+									  : pref64_gen;
+	for (int k = 0; k < 3; ++k) {
+		const SymVariant& sv = tab[pref[k]];
+		if (c->world == 1 || c->own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
 	}
-	// FP64 with general masses: 4 more live doubles (m_i); at 5 CTAs/SM (96 registers) ptxas spills
-	// inside the hot loop (tools/sym_sass_mix.py: 12.0 non-FP64 instructions per pair evaluation
-	// against 6.9 at 4 CTAs/SM), so take the 4-CTA build of the same blocking
-	if (c->prec == 64 && !c->unimass) return tab[1];
-	return tab[0];
+	return tab[pref[2]];
+}
+
+// Which force kernel runs.  Option "pair_symmetry": 1 = the pair-symmetric kernel, 0 = the
+// default kernel (every ordered pair, bit-reproducible), -1 (default) = automatic: the
+// pair-symmetric kernel when the problem is large enough for its 256..1024-row blocks to fill the
+// GPU (measured crossover, profiles/r02_sym_crossover.md) and the exchange allows it.
+constexpr size_t SYM_AUTO_MIN_N = 49152;
+bool sym_in_use(const nbody_ctx* c) {
+	if (c->opt_pair_symmetry == 0) return false;
+	if (c->opt_pair_symmetry > 0) return true;
+	if (c->world > 1 && c->p2p) return false;
+	return c->n >= SYM_AUTO_MIN_N;
 }
 
 // j-slices per launch.  Units (i-tile, j-slice) are handed out dynamically, so the tail is
@@ -300,9 +320,10 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 // Measured at N = 1M (tools/slices_probe.py): 6 / 12 / 20 / 32 / 64 slices = 1093 / 1103 / 1109 /
 // 1111 / 1113 G int/s, i.e. the half-unit tail model; 100 units per CTA (29 slices there) keeps
 // the tail at 0.5 % for 0.9 GB of partial sums per launch (0.1 % of the launch's HBM time).
-unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, long forced) {
+unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, long forced,
+					   unsigned max_slices = MAX_SLICES) {
 	const unsigned UNITS_PER_SLOT = 100, MIN_TILES = 2;
-	unsigned smax = std::min<unsigned>(MAX_SLICES, std::max(1u, jt_count / MIN_TILES));
+	unsigned smax = std::min<unsigned>(max_slices, std::max(1u, jt_count / MIN_TILES));
 	if (forced > 0) return std::min<unsigned>((unsigned)forced, std::max(1u, jt_count));
 	if (n_itiles == 0) return 1;
 	unsigned want = (UNITS_PER_SLOT * slots + n_itiles - 1) / n_itiles;
@@ -325,7 +346,8 @@ struct LaunchPlan {
 };
 
 int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
-	const size_t bytes = (size_t)(lp.s_local + lp.s_remote) * lp.apart_stride * 4 * ctx->esz;
+	// the pair-symmetric kernel adds both sides of every pair into `aj`: no partial-sum rows
+	const size_t bytes = lp.sym ? 0 : (size_t)(lp.s_local + lp.s_remote) * lp.apart_stride * 4 * ctx->esz;
 	if (bytes > ctx->apart_bytes) {
 		CK(cudaStreamSynchronize(ctx->sc));
 		if (ctx->apart) CK(cudaFree(ctx->apart));
@@ -334,7 +356,7 @@ int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
 		CK(cudaMalloc(&ctx->apart, bytes));
 		ctx->apart_bytes = bytes;
 	}
-	ctx->apart_slices = lp.s_local + lp.s_remote;
+	ctx->apart_slices = lp.sym ? 0 : lp.s_local + lp.s_remote;
 	if (lp.sym && lp.rows_pad > ctx->aj_rows) {
 		CK(cudaStreamSynchronize(ctx->sc));
 		if (ctx->aj) CK(cudaFree(ctx->aj));
@@ -375,7 +397,7 @@ uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb, unsign
 }
 
 int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
-	lp->sym = ctx->opt_pair_symmetry != 0;
+	lp->sym = sym_in_use(ctx);
 	if (lp->sym) {
 		const SymVariant& sv = sym_variant_of(ctx);
 		const unsigned TJ = 256, block = sv.threads * sv.ipt;
@@ -403,7 +425,7 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 		lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
 		// shortest walk of a block: tpb * (1 + h) tiles with h >= (nb-1)/2 - (nb even ? 0 : 0)
 		const unsigned min_walk = sym_ntiles(lp->nb, lp->tpb, lp->nb - 1);
-		lp->s_local = choose_slices(lp->nb_own, min_walk, lp->slots, ctx->opt_slices);
+		lp->s_local = choose_slices(lp->nb_own, min_walk, lp->slots, ctx->opt_slices, MAX_SYM_SLICES);
 		lp->s_remote = 0;
 		const int key = (int)(sv.threads * sv.ipt);
 		if (ctx->sym_pairs_key != key) {
@@ -506,7 +528,6 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	const SymVariant& v = sym_variant_of(ctx);
 	SymParams p;
 	p.pos = buf_ptr(ctx, buf);
-	p.apart = ctx->apart;
 	p.aj = ctx->aj;
 	p.rows_pad = lp.rows_pad;
 	p.nb = lp.nb;
@@ -653,7 +674,7 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	p.own0 = ctx->own0;
 	p.own_pad = ctx->own_pad;
 	p.own_real = ctx->own_real;
-	p.n_slices = lp.s_local + lp.s_remote;
+	p.n_slices = lp.sym ? 0 : lp.s_local + lp.s_remote;
 	p.apart_stride = lp.apart_stride;
 	p.aj = lp.sym ? ctx->aj : nullptr;
 	p.aj_stride = lp.rows_pad;
@@ -698,7 +719,7 @@ int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, c
 	p.own0 = ctx->own0;
 	p.own_pad = ctx->own_pad;
 	p.own_real = ctx->own_real;
-	p.n_slices = lp.s_local + lp.s_remote;
+	p.n_slices = lp.sym ? 0 : lp.s_local + lp.s_remote;
 	p.apart_stride = lp.apart_stride;
 	p.aj = lp.sym ? ctx->aj : nullptr;
 	p.aj_stride = lp.rows_pad;
@@ -851,6 +872,16 @@ int ensure_y_gathered(nbody_ctx* ctx) {
 extern "C" {
 
 const char* nbody_version(void) { return "nbody_b200 0.1 (sm_100a)"; }
+
+int nbody_device_count(void) {
+	int ndev = 0, ok = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess) return 0;
+	for (int d = 0; d < ndev; ++d) {
+		cudaDeviceProp prop;
+		if (cudaGetDeviceProperties(&prop, d) == cudaSuccess && prop.major == 10) ++ok;
+	}
+	return ok;
+}
 
 const char* nbody_last_error(const nbody_ctx* ctx) {
 	return ctx ? ctx->err.c_str() : g_err.c_str();
@@ -1092,7 +1123,8 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "variant out of range");
 		ctx->opt_variant = value;
 	} else if (k == "use_graph") ctx->opt_use_graph = value;
-	else if (k == "pair_symmetry") ctx->opt_pair_symmetry = value != 0; else if (k == "sym_variant") {
+	else if (k == "pair_symmetry") ctx->opt_pair_symmetry = value < 0 ? -1 : (value != 0);
+	else if (k == "sym_variant") {
 		const int nv = ctx->prec == 64 ? N_SYM64 : N_SYM32;
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "sym_variant out of range");
 		ctx->opt_sym_variant = value;
@@ -1176,6 +1208,58 @@ int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
 	ctx->tm.total_launches++;
 	CK(cudaStreamSynchronize(ctx->sc));	 // the host buffer is borrowed for the call only
 	return upload_common(ctx);
+}
+
+// Every rank hands over ONLY the rows it owns (own_real x Body<T>, nbody_owned_range); the full
+// position array is assembled on the devices by one all-gather over NVLink instead of every rank
+// pushing all n bodies through PCIe.  Collective: all ranks of the world call it together.
+int nbody_upload_aos_owned(nbody_ctx* ctx, const void* owned_bodies) {
+	if (!ctx || (!owned_bodies && ctx->own_real)) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (ctx->world == 1) return nbody_upload_aos(ctx, owned_bodies);
+	if (ctx->p2p)
+		return fail(ctx, NBODY_ERR_STATE, "nbody_upload_aos_owned needs the NCCL exchange");
+	CK(cudaSetDevice(ctx->device));
+	const size_t bytes = (size_t)ctx->own_real * 7 * ctx->esz;
+	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, ctx->n * 7 * ctx->esz + 64));
+	if (bytes) CK(cudaMemcpyAsync(ctx->d_aos, owned_bodies, bytes, cudaMemcpyHostToDevice, ctx->sc));
+	// equal masses everywhere?  min / max of the masses, all-reduced (MIN over {min, -max})
+	double mm[2] = {HUGE_VAL, HUGE_VAL};
+	for (unsigned i = 0; i < ctx->own_real; ++i) {
+		const double m = ctx->prec == 64 ? ((const double*)owned_bodies)[7 * (size_t)i]
+										  : (double)((const float*)owned_bodies)[7 * (size_t)i];
+		if (!(m == m)) { mm[0] = -HUGE_VAL; mm[1] = -HUGE_VAL; break; }	 // NaN mass: never uniform
+		mm[0] = std::min(mm[0], m);
+		mm[1] = std::min(mm[1], -m);
+	}
+	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 4 * sizeof(double)));
+	CK(cudaMemcpyAsync(ctx->d_norms, mm, sizeof mm, cudaMemcpyHostToDevice, ctx->sc));
+	CKN(g_nccl.AllReduce(ctx->d_norms, ctx->d_norms, 2, NCCL_DOUBLE, NCCL_MIN, ctx->comm, ctx->sc));
+	CK(cudaMemcpyAsync(mm, ctx->d_norms, sizeof mm, cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	const bool uni = ctx->opt_unimass != 0 && mm[0] == -mm[1] && std::isfinite(mm[0]);
+	ctx->unimass = uni;
+	ctx->uniform_mass = uni ? mm[0] : 0.;
+	const unsigned g = (ctx->own_pad + 255) / 256;
+	if (ctx->prec == 64)
+		NB_LAUNCH(pack_aos_owned_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const double*)ctx->d_aos, ctx->Y, ctx->P, ctx->P2, ctx->vel_n, ctx->own0, ctx->own_real,
+				  ctx->own_pad, uni ? 1e150 : 0., uni ? ctx->uniform_mass : 0.);
+	else
+		NB_LAUNCH(pack_aos_owned_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+				  (const float*)ctx->d_aos, ctx->Y, ctx->P, ctx->P2, ctx->vel_n, ctx->own0, ctx->own_real,
+				  ctx->own_pad, uni ? 1e18f : 0.f, uni ? (float)ctx->uniform_mass : 0.f);
+	CK(cudaGetLastError());
+	ctx->tm.total_launches++;
+	CK(cudaStreamSynchronize(ctx->sc));	 // the host buffer is borrowed for the call only
+	ctx->undo_valid = false;
+	ctx->k0_slot = -1;
+	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+	int rc;
+	if ((rc = enqueue_gather(ctx, ctx->Y, ctx->e_gy))) return rc;  // the first force launch waits for it
+	ctx->y_pending = true;
+	ctx->uploaded = true;
+	ctx->tm.steps_done = 0;
+	return NBODY_OK;
 }
 
 int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* v4) {
@@ -1463,7 +1547,12 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 		ctx->timing_pending = false;
 	}
 	ctx->tm.uniform_mass = ctx->unimass ? 1u : 0u;
-	ctx->tm.pair_symmetry = ctx->opt_pair_symmetry ? 1u : 0u;
+	ctx->tm.pair_symmetry = sym_in_use(ctx) ? 1u : 0u;
+	ctx->tm.sym_variant = 0;
+	if (sym_in_use(ctx)) {
+		const SymVariant* tab = ctx->prec == 64 ? g_sym64 : g_sym32;
+		ctx->tm.sym_variant = (uint32_t)(&sym_variant_of(ctx) - tab);
+	}
 	{
 		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;
 		ctx->tm.variant = (ctx->opt_variant < 0 || ctx->opt_variant >= nv) ? 0u : (uint32_t)ctx->opt_variant;
@@ -1564,6 +1653,29 @@ int nbody_download_aos(nbody_ctx* ctx, void* bodies) {
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	CK(cudaMemcpyAsync(bodies, ctx->d_aos, bytes, cudaMemcpyDeviceToHost, ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sc));
+	return NBODY_OK;
+}
+
+// The owned rows only (own_real x Body<T>): no collective, no copy of other ranks' state.
+int nbody_download_aos_owned(nbody_ctx* ctx, void* owned_bodies) {
+	if (!ctx || (!owned_bodies && ctx->own_real)) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	if (!ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "download before upload");
+	CK(cudaSetDevice(ctx->device));
+	if (ctx->own_real) {
+		const size_t bytes = (size_t)ctx->own_real * 7 * ctx->esz;
+		if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, ctx->n * 7 * ctx->esz + 64));
+		const unsigned g = (ctx->own_real + 255) / 256;
+		if (ctx->prec == 64)
+			NB_LAUNCH(unpack_aos_owned_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, (double*)ctx->d_aos, ctx->own0, ctx->own_real);
+		else
+			NB_LAUNCH(unpack_aos_owned_kernel<float>, dim3(g), dim3(256), 0, ctx->sc,
+					  ctx->Y, ctx->vel_n, (float*)ctx->d_aos, ctx->own0, ctx->own_real);
+		CK(cudaGetLastError());
+		ctx->tm.total_launches++;
+		CK(cudaMemcpyAsync(owned_bodies, ctx->d_aos, bytes, cudaMemcpyDeviceToHost, ctx->sc));
+	}
 	CK(cudaStreamSynchronize(ctx->sc));
 	return NBODY_OK;
 }

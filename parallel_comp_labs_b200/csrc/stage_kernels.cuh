@@ -292,6 +292,52 @@ __global__ void pack_aos_kernel(const T* __restrict__ aos, void* Yv, void* Pv, v
 	if (i >= own0 && i < own0 + own_pad) vel[i - own0] = v;
 }
 
+// The same for the OWNED block only (nbody_upload_aos_owned): `aos` holds this rank's own_real
+// bodies; rows own_real..own_pad of the block become pad bodies.  The other ranks' blocks of Y
+// arrive by all-gather over NVLink.  P2 may be null.
+template <typename T>
+__global__ void pack_aos_owned_kernel(const T* __restrict__ aos, void* Yv, void* Pv, void* P2v,
+									  void* velv, unsigned own0, unsigned own_real, unsigned own_pad,
+									  T pad_pos, T pad_mass) {
+	typedef typename V4<T>::type vec4;
+	vec4* Y = reinterpret_cast<vec4*>(Yv);
+	vec4* P = reinterpret_cast<vec4*>(Pv);
+	vec4* P2 = reinterpret_cast<vec4*>(P2v);
+	vec4* vel = reinterpret_cast<vec4*>(velv);
+	const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+	if (li >= own_pad) return;
+	vec4 q, v;
+	if (li < own_real) {
+		const T* b = aos + 7 * (size_t)li;
+		q.x = b[1]; q.y = b[2]; q.z = b[3]; q.w = b[0];
+		v.x = b[4]; v.y = b[5]; v.z = b[6]; v.w = T(0);
+	} else {
+		q.x = q.y = q.z = pad_pos;
+		q.w = pad_mass;
+		v.x = v.y = v.z = v.w = T(0);
+	}
+	const size_t i = (size_t)own0 + li;
+	Y[i] = q;
+	P[i] = q;
+	if (P2) P2[i] = q;
+	vel[li] = v;
+}
+
+// packed -> AoS Body<T> for the owned rows only (nbody_download_aos_owned)
+template <typename T>
+__global__ void unpack_aos_owned_kernel(const void* Yv, const void* velv, T* __restrict__ aos,
+										unsigned own0, unsigned own_real) {
+	typedef typename V4<T>::type vec4;
+	const vec4* Y = reinterpret_cast<const vec4*>(Yv);
+	const vec4* vel = reinterpret_cast<const vec4*>(velv);
+	const unsigned li = blockIdx.x * blockDim.x + threadIdx.x;
+	if (li >= own_real) return;
+	const vec4 q = Y[(size_t)own0 + li], v = vel[li];
+	T* b = aos + 7 * (size_t)li;
+	b[0] = q.w; b[1] = q.x; b[2] = q.y; b[3] = q.z;
+	b[4] = v.x; b[5] = v.y; b[6] = v.z;
+}
+
 // lab_5 SoA (T m[n], T3 r[n], T3 v[n]) -> packed
 template <typename T>
 __global__ void pack_soa_kernel(const T* __restrict__ m, const void* r4v, const void* v4v,

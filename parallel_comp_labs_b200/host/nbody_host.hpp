@@ -20,6 +20,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <fstream>
@@ -350,7 +351,7 @@ struct RunOptions {
 	std::string tableau;	 // "" = `scheme`; else a name from nbody_tableaux.hpp (nbody_step_rk)
 	double adaptive_rtol = 0;  // > 0: step-size control over the embedded pair `tableau`, tau = first step
 	double adaptive_atol = 0;
-	bool pair_symmetry = false;	 // opt-in: evaluate each pair once (one GPU), see include/nbody_b200.h
+	long pair_symmetry = -1;  // -1 auto (library default), 0 one-sided bit-reproducible kernel, 1 pair-symmetric
 	bool report = false;
 };
 
@@ -386,6 +387,18 @@ class Solver_N_body {
 		const int world = opt.n_gpus;
 		if ((std::size_t)world > n)	 // class_Solver_N_body.hpp:115-117
 			throw "The number of processes is greater than the problem dimension";
+		// Everything that can fail without a GPU call is checked BEFORE ranks are spawned: a rank
+		// that returns early would leave its peers waiting in the communicator set-up forever.
+		if (world < 1) throw std::runtime_error("--gpus must be >= 1");
+		if (world > nbody_device_count())
+			throw std::runtime_error("--gpus " + std::to_string(world) + " but only " +
+									 std::to_string(nbody_device_count()) + " sm_100 device(s) are visible");
+		if (!opt.tableau.empty()) {
+			const nbody_host::Tableau* tab = nbody_host::find_tableau(opt.tableau);
+			if (!tab) throw std::runtime_error("unknown tableau " + opt.tableau);
+			if (opt.adaptive_rtol > 0 && !tab->embedded)
+				throw std::runtime_error("tableau " + opt.tableau + " has no embedded companion");
+		}
 		char uid[NBODY_NCCL_UID_BYTES] = {};
 		if (world > 1 && nbody_nccl_unique_id(uid) != NBODY_OK)
 			throw std::runtime_error(std::string("NCCL: ") + nbody_last_error(nullptr));
@@ -408,15 +421,25 @@ class Solver_N_body {
 		const int prec = std::is_same<T, double>::value ? 64 : 32;
 		if (nbody_create(&ctx, n, prec, rank, rank, world, world > 1 ? uid : nullptr) != NBODY_OK) {
 			error = std::string("nbody_create: ") + nbody_last_error(nullptr);
+			if (world > 1) {  // peers are waiting in ncclCommInitRank for this rank
+				std::cerr << "rank " << rank << ": " << error << std::endl;
+				std::_Exit(3);
+			}
 			return;
 		}
 		auto fail = [&](const char* what) {
 			error = std::string(what) + ": " + nbody_last_error(ctx);
+			if (world > 1) {
+				// peers may already be blocked in a collective that this rank will never join:
+				// report and end the process instead of hanging in join()
+				std::cerr << "rank " << rank << ": " << error << std::endl;
+				std::_Exit(3);
+			}
 			nbody_destroy(ctx);
 		};
 		if (nbody_set_params(ctx, (double)sys.G, (double)sys.eps)) return fail("set_params");
 		if (opt.variant >= 0 && nbody_set_option(ctx, "variant", opt.variant)) return fail("variant");
-		if (opt.pair_symmetry && nbody_set_option(ctx, "pair_symmetry", 1)) return fail("pair_symmetry");
+		if (nbody_set_option(ctx, "pair_symmetry", opt.pair_symmetry)) return fail("pair_symmetry");
 		if (nbody_upload_aos(ctx, sys.traj_init.data())) return fail("upload");
 
 		std::ofstream traj;

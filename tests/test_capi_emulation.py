@@ -203,8 +203,9 @@ def test_emulated_abi_python_host_mirror_writes_reference_rows(golden, tmp_path)
     # (the reference's own first row, reproduced here digit for digit)
 
 
-def _run_ranks(world, bodies, eps, tau, steps, **options):
-    """One emulated context per rank, ranks as threads (tests/tools/fake_nccl.cpp)."""
+def _run_ranks(world, bodies, eps, tau, steps, owned_io=False, **options):
+    """One emulated context per rank, ranks as threads (tests/tools/fake_nccl.cpp).
+    owned_io: every rank uploads / downloads only the rows it owns (nbody_upload_aos_owned)."""
     import threading
     n = bodies.shape[0]
     uid = capi.nccl_unique_id()
@@ -216,13 +217,18 @@ def _run_ranks(world, bodies, eps, tau, steps, **options):
                 ctx.set_params(6.67e-11, eps)
                 for k, v in options.items():
                     ctx.set_option(k, v)
-                ctx.upload_aos(bodies)
-                acc = ctx.rhs()
                 b, e = ctx.owned_range()
+                if owned_io:
+                    ctx.upload_aos_owned(bodies[b:e])
+                else:
+                    ctx.upload_aos(bodies)
+                acc = ctx.rhs()
                 ctx.step(capi.NBODY_RK4, tau, steps)
                 snap = ctx.snapshot() if r == 0 else None       # not a collective
                 fin = ctx.download_aos()
-                out[r] = dict(acc=acc, rows=(b, e), fin=fin, snap=snap, diag=ctx.diagnostics())
+                own = ctx.download_aos_owned() if owned_io else fin[b:e]
+                out[r] = dict(acc=acc, rows=(b, e), fin=fin, snap=snap, diag=ctx.diagnostics(),
+                              own=own, tm=ctx.timing())
         except Exception as ex:                                  # noqa: BLE001
             errs.append((r, repr(ex)))
     threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
@@ -232,6 +238,22 @@ def _run_ranks(world, bodies, eps, tau, steps, **options):
         t.join(600)
     assert not errs and all(o is not None for o in out), errs
     return out
+
+
+@pytest.mark.parametrize("equal_masses", [True, False])
+def test_emulated_abi_owned_rows_upload_and_download(oracle, equal_masses):
+    """nbody_upload_aos_owned / nbody_download_aos_owned on 3 ranks: each rank hands over only its
+    block, the array is assembled by all-gather, equal masses are detected across ranks."""
+    n = 900
+    b = generators.plummer_bodies(n, seed=23) if equal_masses else generators.uniform_bodies(n, seed=23)
+    eps, tau = (1e-3, 1e-3) if equal_masses else (1e-6, 0.1)
+    want, _ = oracle.rk4(b, tau, 0.0, 1.0, eps=eps, max_steps=2, rows=False, threads=8)
+    res = _run_ranks(3, b, eps, tau, 2, owned_io=True)
+    for o in res:
+        lo, hi = o["rows"]
+        assert o["tm"].uniform_mass == (1 if equal_masses else 0)
+        check_state(o["fin"], want, b, 1e-10)
+        assert np.array_equal(o["own"], o["fin"][lo:hi])
 
 
 @pytest.mark.parametrize("world,opts", [(2, {}), (3, {}), (2, {"pair_symmetry": 1}),

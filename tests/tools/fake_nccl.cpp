@@ -47,6 +47,7 @@ void sum_into(T* out, const std::vector<const void*>& send, size_t offset, size_
 		for (size_t r = 1; r < send.size(); ++r) {	// rank order: deterministic
 			const T v = static_cast<const T*>(send[r])[offset + k];
 			if (op == 0) s += v;
+			else if (op == 3) { if (v < s || v != v) s = v; }  // ncclMin
 			else if (v > s || v != v) s = v;  // ncclMax (NaN wins, as it must stay visible)
 		}
 		out[k] = s;
@@ -110,7 +111,7 @@ int ncclAllGather(const void* send, void* recv, size_t count, int dt, ncclComm_t
 }
 
 int ncclAllReduce(const void* send, void* recv, size_t count, int dt, int op, ncclComm_t c, void*) {
-	if ((op != 0 && op != 2) || (dt != 8 && dt != 7)) return 4;	 // ncclSum, ncclMax
+	if ((op != 0 && op != 2 && op != 3) || (dt != 8 && dt != 7)) return 4;	 // ncclSum, ncclMax, ncclMin
 	Group* g = c->g;
 	g->send[c->rank] = send;
 	g->barrier();

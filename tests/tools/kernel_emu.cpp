@@ -116,9 +116,7 @@ int rhs_impl(unsigned n, const double* bodies, double G, double eps, int sym, in
 		p.pad_pos = (double)pad_pos;
 		apart_stride = p.rows_pad;
 		aj_stride = p.rows_pad;
-		apart.assign((size_t)slices * p.rows_pad, vec4{(T)NAN, (T)NAN, (T)NAN, (T)NAN});
 		aj.assign((size_t)3 * p.rows_pad, T(0));  // cudaMemsetAsync before the launch
-		p.apart = apart.data();
 		p.aj = aj.data();
 		const unsigned g = std::min(p.nb * slices, grid);
 		switch (ipt * 2 + (um ? 1 : 0)) {
@@ -144,7 +142,7 @@ int rhs_impl(unsigned n, const double* bodies, double G, double eps, int sym, in
 	sp.own0 = 0;
 	sp.own_pad = own_pad;
 	sp.own_real = n;
-	sp.n_slices = slices;
+	sp.n_slices = sym ? 0 : slices;	 // the pair-symmetric kernel adds both sides into aj
 	sp.apart_stride = apart_stride;
 	sp.aj = sym ? aj.data() : nullptr;
 	sp.aj_stride = aj_stride;
@@ -183,11 +181,9 @@ int rhs_sym_ranks(unsigned n, const double* bodies, double G, double eps, unsign
 		});
 		unsigned counter = 0;
 		std::vector<T> aj((size_t)3 * n_pad, 0.);
-		apart[r].assign((size_t)n_slices * own_pad, vec4{NAN, NAN, NAN, NAN});
 		SymParams p;
 		memset(&p, 0, sizeof(p));
 		p.pos = Y.data();
-		p.apart = apart[r].data();
 		p.aj = aj.data();
 		p.rows_pad = nb * BLOCK;
 		p.nb = nb;
@@ -217,7 +213,7 @@ int rhs_sym_ranks(unsigned n, const double* bodies, double G, double eps, unsign
 		sp.own0 = own0;
 		sp.own_pad = own_pad;
 		sp.own_real = own_real;
-		sp.n_slices = n_slices;
+		sp.n_slices = 0;
 		sp.apart_stride = nb_own * BLOCK;
 		sp.aj = aj_sum.data();
 		sp.aj_stride = nb * BLOCK;

@@ -59,8 +59,15 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
                 res[f"rk{scheme}_snap"] = float(np.abs(snap - fin[:, 1:4]).max())
                 ko, uo = o.energy(w, eps=eps, threads=4)
                 res[f"rk{scheme}_E"] = abs((k + u) - (ko + uo)) / abs(ko + uo)
+                if not P2P:
+                    # the same run with every rank moving only the rows it owns through PCIe
+                    ctx.upload_aos_owned(bodies[b:e].astype(np.float64 if prec == 64 else np.float32))
+                    ctx.step(scheme, tau, 3)
+                    own = ctx.download_aos_owned().astype(np.float64)
+                    res[f"rk{scheme}_owned"] = (float(np.abs(own - fin[b:e]).max()
+                                                      / np.abs(fin[:, 1:]).max()) if e > b else 0.0)
             lim = {"rhs": tol, "_r": tol, "_dv": max(tol * 10, dv_floor), "_snap": 0.0 if prec == 64 else 1e-6,
-                   "_E": max(tol * 10, 1e-9)}
+                   "_E": max(tol * 10, 1e-9), "_owned": tol if PAIR_SYM else 0.0}
             good = all(v <= next(l for suf, l in lim.items() if k_.endswith(suf))
                        for k_, v in res.items())
             ok &= good
