@@ -49,6 +49,10 @@ def lib() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
+    path = os.environ.get("NBODY_B200_LIB", LIB_PATH)   # e.g. the bounds-checked build (make check)
+    if path != LIB_PATH:
+        _lib = _bind(C.CDLL(path))
+        return _lib
     if not os.path.exists(LIB_PATH):
         raise NBodyError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
                          f"g.build()'` (or make -C parallel_comp_labs_b200/csrc). "

@@ -34,6 +34,17 @@
 #endif
 #include <stdint.h>
 
+// Device-side bounds asserts (compute-sanitizer is closed on the GPU pool): with
+// -DNBODY_BOUNDS_CHECK every global store / RED / bulk-copy source of K1, K1s and K2 checks its
+// index against the allocation and traps (the host then sees a launch failure).  The product
+// build compiles them out (SASS unchanged); `make -C parallel_comp_labs_b200/csrc check` builds
+// libnbody_b200_check.so, which the -m gpu suite can be pointed at with NBODY_B200_LIB.
+#if defined(NBODY_BOUNDS_CHECK) && !defined(NBODY_HOST_EMU)
+#define NB_CHECK(cond) do { if (!(cond)) __trap(); } while (0)
+#else
+#define NB_CHECK(cond) do { } while (0)
+#endif
+
 namespace nbody {
 
 template <typename T> struct V4;
@@ -230,6 +241,7 @@ struct ForceParams {
 	unsigned slice_base;   // first slice row of apart written by this launch
 	unsigned n_real;	   // bodies that exist; rows >= n_real of `pos` are padding
 	unsigned* counter;	   // work-unit ticket counter, zeroed before the launch
+	unsigned apart_rows;   // rows allocated in apart (bounds asserts only)
 };
 
 template <typename T> struct Tile {
@@ -239,6 +251,7 @@ template <typename T> struct Tile {
 // global address of j-tile `jt` (absolute tile index): block of its owner + offset inside it
 template <typename vec4, int TJ>
 __device__ __forceinline__ const vec4* tile_src(const ForceParams& p, unsigned jt) {
+	NB_CHECK(jt < p.jt_total);
 	if (p.contiguous) return reinterpret_cast<const vec4*>(p.blk[0]) + (size_t)jt * TJ;
 	const unsigned r = jt / p.jt_per_rank;
 	return reinterpret_cast<const vec4*>(p.blk[r]) + (size_t)(jt - r * p.jt_per_rank) * TJ;
@@ -359,7 +372,10 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			o.y = ry[k];
 			o.z = rz[k];
 			o.w = T(0);
-			if (row0 + k * THREADS < p.own_pad) out[row0 + k * THREADS] = o;
+			if (row0 + k * THREADS < p.own_pad) {
+				NB_CHECK((size_t)(p.slice_base + slice) * p.own_pad + row0 + k * THREADS < p.apart_rows);
+				out[row0 + k * THREADS] = o;
+			}
 		}
 		if (tid == 0) *next_unit_s = next_ticket;
 		__syncthreads();

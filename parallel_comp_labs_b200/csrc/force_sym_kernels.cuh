@@ -80,6 +80,7 @@ struct SymParams {
 	unsigned n_slices;	 // slices of a block's walk
 	unsigned* counter;	 // work-unit ticket counter, zeroed before the launch
 	double pad_pos;		 // coordinates given to i-rows >= n_pad (see pack_aos_kernel)
+	unsigned pos_rows;	 // rows allocated in pos (bounds asserts only)
 };
 
 // One j-body (travelling with its accumulator) against the I i-bodies of this thread.
@@ -212,6 +213,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 				const unsigned st = (ring + k) % STAGES;
 				bool d;
 				const unsigned jt = sym_tile(p.nb, TPB, a, t0 + k, &d);
+				NB_CHECK((size_t)(jt + 1) * TJ <= p.pos_rows);
 				mbar_expect_tx(&full[st], TILE_BYTES);
 				bulk_g2s(tiles + (size_t)st * TJ, pos + (size_t)jt * TJ, TILE_BYTES, &full[st]);
 			}
@@ -270,6 +272,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 																	  mi, loc, ajx, ajy, ajz, cl, mn,
 																	  next_lane);
 					const unsigned j = j_first + (unsigned)s0 + (unsigned)(tid & 31);
+					NB_CHECK(j < p.rows_pad);
 					atomicAdd(gjx + j, ajx);  // result unused -> RED.ADD
 					atomicAdd(gjy + j, ajy);
 					atomicAdd(gjz + j, ajz);
@@ -286,6 +289,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			if (tid == 0 && t + STAGES < ntiles) {
 				bool d;
 				const unsigned nt = sym_tile(p.nb, TPB, a, t0 + t + STAGES, &d);
+				NB_CHECK((size_t)(nt + 1) * TJ <= p.pos_rows);
 				mbar_expect_tx(&full[st], TILE_BYTES);
 				bulk_g2s(tiles + (size_t)st * TJ, pos + (size_t)nt * TJ, TILE_BYTES, &full[st]);
 			}
@@ -298,6 +302,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
 		for (int k = 0; k < I; ++k) {
 			const unsigned row = row0 + k * THREADS;	 // < rows_pad = nb * BLOCK
+			NB_CHECK(row < p.rows_pad);
 			atomicAdd(gjx + row, accm[(0 * I + k) * THREADS + tid]);  // result unused -> RED.ADD
 			atomicAdd(gjy + row, accm[(1 * I + k) * THREADS + tid]);
 			atomicAdd(gjz + row, accm[(2 * I + k) * THREADS + tid]);

@@ -499,6 +499,7 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 	p.slice_base = slice_base;
 	p.n_real = (unsigned)ctx->n;
 	p.counter = ctx->d_counters + (slice_base ? 1 : 0);
+	p.apart_rows = (unsigned)std::min<size_t>(ctx->apart_bytes / (4 * ctx->esz), 0xffffffffu);
 	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
 	const unsigned long long units = (unsigned long long)lp.n_itiles * n_slices;
 	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
@@ -539,6 +540,7 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.n_slices = lp.s_local;
 	p.counter = ctx->d_counters;
 	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
+	p.pos_rows = ctx->n_pad + SYM_EXTRA_TILES * PAD_UNIT;
 	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
 	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
 	const unsigned long long units = (unsigned long long)lp.nb_own * lp.s_local;

@@ -390,9 +390,10 @@ class Solver_N_body {
 		// Everything that can fail without a GPU call is checked BEFORE ranks are spawned: a rank
 		// that returns early would leave its peers waiting in the communicator set-up forever.
 		if (world < 1) throw std::runtime_error("--gpus must be >= 1");
-		if (world > nbody_device_count())
+		if (world > 1 && world > nbody_device_count())	// (one rank: nbody_create reports it)
 			throw std::runtime_error("--gpus " + std::to_string(world) + " but only " +
-									 std::to_string(nbody_device_count()) + " sm_100 device(s) are visible");
+									 std::to_string(nbody_device_count()) +
+									 " sm_100 device(s) are visible (no CPU fallback)");
 		if (!opt.tableau.empty()) {
 			const nbody_host::Tableau* tab = nbody_host::find_tableau(opt.tableau);
 			if (!tab) throw std::runtime_error("unknown tableau " + opt.tableau);

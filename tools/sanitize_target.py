@@ -12,7 +12,8 @@ sizes = [int(s) for s in (sys.argv[1:] or ["257", "3000"])]
 for n in sizes:
     uni = generators.uniform_bodies(n, seed=11)          # general masses
     plu = generators.plummer_bodies(n, seed=12)          # equal masses
-    plu[1, 1:4] = plu[0, 1:4] + 1e-5                      # inside the clamp radius: redo path
+    if n > 1:
+        plu[1, 1:4] = plu[0, 1:4] + 1e-5                   # inside the clamp radius: redo path
     for prec in (64, 32):
         for bodies, eps in ((uni, 1e-6), (plu, 1e-3)):
             with capi.Context(n, prec) as ctx:
