@@ -56,6 +56,9 @@ def parse():
     ap.add_argument("--sym-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
+    ap.add_argument("--trace-out", default="",
+                    help="write a per-rank operation list (CUDA-event times of one extra, untimed step: "
+                         "force launches, stage kernels, memsets, all-gathers, reduce-scatters) to this JSON file")
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the 2-step general-mass (unimass=0) figure")
     ap.add_argument("--no-parity", action="store_true",
@@ -371,6 +374,23 @@ def run_b200(args):
             e2e_ms.append(max_over_ranks(dt))
     e2e_value = stages * float(n) * float(n) * len(e2e_ms) / (sum(e2e_ms) * 1e-3) / 1e9
     bytes_io = n * 7 * np.dtype(dtype).itemsize * (world if (world > 1 and args.p2p) else 1)
+    # ---- per-rank operation list of one extra step (untimed; the library's own event pairs) ----
+    if args.trace_out:
+        ctx.set_option("trace", 1)
+        barrier()
+        ctx.step(scheme, tau, 1)
+        ctx.sync()
+        mine = {"rank": rank, "step_ms": ctx.timing().last_call_ms, "ops": ctx.trace()}
+        ctx.set_option("trace", 0)
+        if world > 1:
+            allr = [None] * world
+            dist.all_gather_object(allr, mine)
+        else:
+            allr = [mine]
+        if rank == 0:
+            with open(args.trace_out, "w") as f:
+                json.dump({"workload": workload_config(args, tau, eps, None)["workload"], "n_gpus": world,
+                           "ranks": allr}, f, indent=1)
     # ---- parity of THIS run's configuration (every rank checks rows it owns; not timed) -------
     parity = None
     if not args.no_parity:

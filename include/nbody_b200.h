@@ -57,6 +57,19 @@ typedef struct nbody_timing {
 	uint32_t sym_variant;		 /* pair-symmetric kernel variant index in use (0 if not in use) */
 } nbody_timing;
 
+/* Option "trace" = 1: every operation a call enqueues (force launch, fused stage kernel, memsets,
+ * all-gather, reduce-scatter) is bracketed by a CUDA-event pair on its stream; nbody_get_trace
+ * returns them for the LAST nbody_step* / nbody_rhs call, times relative to the start of the call.
+ * A per-rank launch list without a profiler (ncu cannot be run under a multi-rank job). */
+enum { NBODY_TRACE_FORCE = 0, NBODY_TRACE_STAGE = 1, NBODY_TRACE_MEMSET = 2, NBODY_TRACE_GATHER = 3,
+	   NBODY_TRACE_REDUCE = 4 };
+typedef struct nbody_trace_entry {
+	uint32_t kind;	 /* NBODY_TRACE_* */
+	uint32_t stream; /* 0 compute, 1 comm */
+	double start_ms; /* after the call began on the compute stream */
+	double dur_ms;
+} nbody_trace_entry;
+
 /* Fills out[NBODY_NCCL_UID_BYTES] with a fresh NCCL unique id (rank 0 calls this and
  * distributes the bytes; replaces MPI_Init's rendezvous, lab_4 N_body.cpp:67).  One id
  * creates ONE communicator: every nbody_create of a world needs a fresh id. */
@@ -210,6 +223,8 @@ int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential);
 int nbody_diagnostics(nbody_ctx* ctx, double out[9]);
 
 int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out);
+/* Up to `cap` entries of the last call's trace (option "trace"); *n_out = entries recorded. Syncs. */
+int nbody_get_trace(nbody_ctx* ctx, nbody_trace_entry* out, size_t cap, size_t* n_out);
 
 /* Pinned host memory for callers that want zero-staging transfers. */
 void* nbody_host_alloc(size_t bytes);

@@ -36,6 +36,14 @@ class Timing(C.Structure):
                 ("sym_variant", C.c_uint32)]
 
 
+class TraceEntry(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("stream", C.c_uint32), ("start_ms", C.c_double),
+                ("dur_ms", C.c_double)]
+
+
+TRACE_KINDS = ("force", "stage", "memset", "all_gather", "reduce_scatter")
+
+
 def build_library(quiet: bool = True) -> None:
     subprocess.run(["make", "-C", os.path.join(PKG_DIR, "csrc")], check=True,
                    stdout=subprocess.DEVNULL if quiet else None)
@@ -100,6 +108,7 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_energy.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.nbody_diagnostics.argtypes = [vp, C.POINTER(C.c_double)]
     L.nbody_get_timing.argtypes = [vp, C.POINTER(Timing)]
+    L.nbody_get_trace.argtypes = [vp, C.POINTER(TraceEntry), sz, C.POINTER(sz)]
     L.nbody_host_alloc.restype = vp
     L.nbody_host_alloc.argtypes = [sz]
     L.nbody_host_free.argtypes = [vp]
@@ -337,6 +346,14 @@ class Context:
         return {"kinetic": v[0], "potential": v[1], "momentum": np.array(v[2:5]),
                 "mass_moment": np.array(v[5:8]), "mass": v[8],
                 "com": np.array(v[5:8]) / v[8] if v[8] else np.zeros(3)}
+
+    def trace(self, cap: int = 4096) -> list[dict]:
+        """Operations of the last call (option "trace" = 1): kind, stream, start_ms, dur_ms."""
+        buf = (TraceEntry * cap)()
+        n = C.c_size_t()
+        self._ck(self.L.nbody_get_trace(self.h, buf, cap, C.byref(n)))
+        return [{"kind": TRACE_KINDS[buf[k].kind], "stream": "compute" if buf[k].stream == 0 else "comm",
+                 "start_ms": buf[k].start_ms, "dur_ms": buf[k].dur_ms} for k in range(min(n.value, cap))]
 
     def timing(self) -> Timing:
         t = Timing()

@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 	constexpr int BLOCK = THREADS * I;
 	static_assert(BLOCK % TJ == 0, "a block must be a whole number of j-tiles");
 	constexpr unsigned TPB = BLOCK / TJ;
+	constexpr unsigned SPT = TJ / 32;  // strips per tile
 	constexpr uint32_t TILE_BYTES = TJ * sizeof(vec4);
 	constexpr size_t ACC_BYTES = (size_t)3 * I * THREADS * sizeof(T);
 
@@ -202,8 +203,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
 		const unsigned a_loc = unit / p.n_slices;
 		const unsigned slice = unit - a_loc * p.n_slices;
 		const unsigned a = p.block0 + a_loc;
-		unsigned t0, t1;
-		sym_slice_range(sym_ntiles(p.nb, TPB, a), p.n_slices, slice, &t0, &t1);
+		unsigned q0, q1, t0, t1;  // strips of the walk this unit takes, and the tiles they lie in
+		sym_slice_range(sym_ntiles(p.nb, TPB, a), SPT, p.n_slices, slice, &q0, &q1);
+		sym_slice_tiles(SPT, q0, q1, &t0, &t1);
 		const unsigned ntiles = t1 - t0;
 
 		// prologue: the ring is empty here (previous unit ended with __syncthreads)
@@ -246,7 +248,11 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			const unsigned jt = sym_tile(p.nb, TPB, a, t0 + t, &diag);
 			const unsigned j_first = jt * TJ;
 			// bodies of this tile that exist (0 for pad-only and phantom tiles)
-			const int cnt = j_first >= p.n_real ? 0 : (int)min((unsigned)TJ, p.n_real - j_first);
+			int cnt = j_first >= p.n_real ? 0 : (int)min((unsigned)TJ, p.n_real - j_first);
+			unsigned part_lo, part_hi;	// the bodies of this tile that belong to the unit's strips
+			sym_tile_part(t0 + t, SPT, q0, q1, &part_lo, &part_hi);
+			const int lo = (int)part_lo;
+			cnt = min(cnt, (int)part_hi);
 			Acc<T, I> loc;
 			int mn;
 			if (diag) {
@@ -254,7 +260,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 #pragma unroll
 				for (int k = 0; k < I; ++k) loc.x[k] = loc.y[k] = loc.z[k] = T(0);
 #pragma unroll 2
-				for (int jj = 0; jj < cnt; ++jj)
+				for (int jj = lo; jj < cnt; ++jj)
 					interact<T, I, ORD, UM != 0, true>(tile[jj], xi, yi, zi, loc, cl, mn);
 #pragma unroll
 				for (int k = 0; k < I; ++k) {
@@ -263,7 +269,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
 					accm[(2 * I + k) * THREADS + tid] += loc.z[k];
 				}
 			} else {
-				for (int s0 = 0; s0 < cnt; s0 += 32) {	// strips that hold a real body
+				for (int s0 = lo; s0 < cnt; s0 += 32) {	// strips that hold a real body
 					T ajx, ajy, ajz;
 					sym_strip<T, I, ORD, UM != 0, false, ROT != 0>(tile + s0, tid & 31, xi, yi, zi, mi,
 																   loc, ajx, ajy, ajz, cl, mn, next_lane);

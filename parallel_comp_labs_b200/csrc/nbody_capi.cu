@@ -217,6 +217,11 @@ struct nbody_ctx {
 				ev_stop = nullptr;
 	std::vector<cudaEvent_t> kev;  // pairs around force launches (time_kernels)
 	size_t kev_used = 0;
+	// option "trace": event pairs around every operation of a call (nbody_get_trace)
+	struct TraceEv { uint32_t kind, stream; cudaEvent_t e0, e1; };
+	std::vector<TraceEv> tev;
+	size_t tev_used = 0;
+	long opt_trace = 0;
 	ncclComm_t comm = nullptr;
 	// peer-pull exchange (nbody_p2p_connect): remote j-tiles are fetched from the peers' HBM by
 	// the force kernel's bulk-async copies; no all-gather on the step path
@@ -267,6 +272,24 @@ int fail(nbody_ctx* c, int code, const std::string& msg) {
 			return fail(ctx, NBODY_ERR_NCCL, std::string(#call) + ": " +                      \
 												 g_nccl.GetErrorString(r__));                 \
 	} while (0)
+
+// option "trace": bracket one enqueued operation with an event pair on its stream
+int trace_begin(nbody_ctx* ctx, cudaStream_t st, uint32_t kind) {
+	if (!ctx->opt_trace) return -1;
+	if (ctx->tev_used == ctx->tev.size()) {
+		nbody_ctx::TraceEv t{kind, 0, nullptr, nullptr};
+		if (cudaEventCreate(&t.e0) != cudaSuccess || cudaEventCreate(&t.e1) != cudaSuccess) return -1;
+		ctx->tev.push_back(t);
+	}
+	nbody_ctx::TraceEv& t = ctx->tev[ctx->tev_used];
+	t.kind = kind;
+	t.stream = st == ctx->sc ? 0u : st == ctx->sm ? 1u : 2u;
+	cudaEventRecord(t.e0, st);
+	return (int)ctx->tev_used++;
+}
+void trace_end(nbody_ctx* ctx, cudaStream_t st, int idx) {
+	if (idx >= 0) cudaEventRecord(ctx->tev[idx].e1, st);
+}
 
 // variant -1 (default) = entry 0 of the table.
 const Variant& variant_of(const nbody_ctx* c) {
@@ -425,7 +448,9 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 		lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
 		// shortest walk of a block: tpb * (1 + h) tiles with h >= (nb-1)/2 - (nb even ? 0 : 0)
 		const unsigned min_walk = sym_ntiles(lp->nb, lp->tpb, lp->nb - 1);
-		lp->s_local = choose_slices(lp->nb_own, min_walk, lp->slots, ctx->opt_slices, MAX_SYM_SLICES);
+		// slices are cut at strip granularity (32 j-bodies; sym_schedule.h), at least 2 strips each
+		lp->s_local = choose_slices(lp->nb_own, min_walk * (TJ / 32), lp->slots, ctx->opt_slices,
+									MAX_SYM_SLICES);
 		lp->s_remote = 0;
 		const int key = (int)(sv.threads * sv.ipt);
 		if (ctx->sym_pairs_key != key) {
@@ -500,7 +525,11 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 	p.n_real = (unsigned)ctx->n;
 	p.counter = ctx->d_counters + (slice_base ? 1 : 0);
 	p.apart_rows = (unsigned)std::min<size_t>(ctx->apart_bytes / (4 * ctx->esz), 0xffffffffu);
-	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
+	{
+		const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_MEMSET);
+		CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
+		trace_end(ctx, ctx->sc, tr);
+	}
 	const unsigned long long units = (unsigned long long)lp.n_itiles * n_slices;
 	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -516,7 +545,9 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 		e1 = ctx->kev[ctx->kev_used++];
 		CK(cudaEventRecord(e0, ctx->sc));
 	}
+	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_FORCE);
 	v.launch[ctx->unimass ? 1 : 0](dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
+	trace_end(ctx, ctx->sc, tr);
 	CK(cudaGetLastError());
 	if (e1) CK(cudaEventRecord(e1, ctx->sc));
 	ctx->tm.force_launches++;
@@ -541,8 +572,12 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.counter = ctx->d_counters;
 	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
 	p.pos_rows = ctx->n_pad + SYM_EXTRA_TILES * PAD_UNIT;
-	CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
-	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
+	{
+		const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_MEMSET);
+		CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
+		CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
+		trace_end(ctx, ctx->sc, tr);
+	}
 	const unsigned long long units = (unsigned long long)lp.nb_own * lp.s_local;
 	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -558,7 +593,9 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 		e1 = ctx->kev[ctx->kev_used++];
 		CK(cudaEventRecord(e0, ctx->sc));
 	}
+	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_FORCE);
 	v.launch[ctx->unimass ? 1 : 0](dim3(grid), ctx->sc, v.smem, p, ctx->eps * ctx->eps);
+	trace_end(ctx, ctx->sc, tr);
 	CK(cudaGetLastError());
 	if (e1) CK(cudaEventRecord(e1, ctx->sc));
 	ctx->tm.force_launches++;
@@ -567,6 +604,7 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 		// every rank has collected reactions for ALL bodies its walk touched: sum them over the
 		// ranks, each rank keeping the rows it owns (in place: rows_pad == world * own_pad here)
 		const int dt = ctx->prec == 64 ? NCCL_DOUBLE : NCCL_FLOAT;
+		const int tr2 = trace_begin(ctx, ctx->sc, NBODY_TRACE_REDUCE);
 		CKN(g_nccl.GroupStart());
 		for (int c = 0; c < 3; ++c) {
 			char* base = (char*)ctx->aj + (size_t)c * lp.rows_pad * ctx->esz;
@@ -574,6 +612,7 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 									 ctx->own_pad, dt, NCCL_SUM, ctx->comm, ctx->sc));
 		}
 		CKN(g_nccl.GroupEnd());
+		trace_end(ctx, ctx->sc, tr2);
 	}
 	return NBODY_OK;
 }
@@ -585,8 +624,10 @@ int enqueue_gather(nbody_ctx* ctx, void* buf, cudaEvent_t done) {
 	CK(cudaStreamWaitEvent(ctx->sm, ctx->e_k2, 0));
 	const size_t bytes = (size_t)ctx->own_pad * 4 * ctx->esz;
 	char* base = (char*)buf;
+	const int tr = trace_begin(ctx, ctx->sm, NBODY_TRACE_GATHER);
 	CKN(g_nccl.AllGather(base + (size_t)ctx->rank * bytes, base, bytes, NCCL_INT8, ctx->comm,
 						 ctx->sm));
+	trace_end(ctx, ctx->sm, tr);
 	CK(cudaEventRecord(done, ctx->sm));
 	return NBODY_OK;
 }
@@ -688,7 +729,9 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	p.first = first;
 	p.last = last;
 	auto kern = stage_kernel<T>;
+	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_STAGE);
 	NB_LAUNCH(kern, dim3((ctx->own_real + 255) / 256), dim3(256), 0, ctx->sc, p);
+	trace_end(ctx, ctx->sc, tr);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
@@ -744,7 +787,9 @@ int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, c
 		g.e[j] = (g.want_err && j <= s) ? (T)k.e[j] : T(0);
 	}
 	auto kern = stage_general_kernel<T>;
+	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_STAGE);
 	NB_LAUNCH(kern, dim3((ctx->own_real + 255) / 256), dim3(256), 0, ctx->sc, g);
+	trace_end(ctx, ctx->sc, tr);
 	CK(cudaGetLastError());
 	ctx->tm.total_launches++;
 	return NBODY_OK;
@@ -926,6 +971,7 @@ void nbody_destroy(nbody_ctx* ctx) {
 		if (ctx->snap_ev[s]) cudaEventDestroy(ctx->snap_ev[s]);
 	}
 	for (cudaEvent_t e : ctx->kev) cudaEventDestroy(e);
+	for (auto& t : ctx->tev) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
 	cudaEvent_t evs[] = {ctx->e_k2, ctx->e_g, ctx->e_gy, ctx->e_snap, ctx->ev_start, ctx->ev_stop};
 	for (cudaEvent_t e : evs)
 		if (e) cudaEventDestroy(e);
@@ -1119,6 +1165,7 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 	if (!ctx || !name) return fail(ctx, NBODY_ERR_ARG, "null argument");
 	std::string k(name);
 	if (k == "time_kernels") ctx->opt_time_kernels = value;
+	else if (k == "trace") ctx->opt_trace = value != 0;
 	else if (k == "slices") ctx->opt_slices = value;
 	else if (k == "variant") {
 		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;
@@ -1305,6 +1352,7 @@ static int begin_timed_call(nbody_ctx* ctx) {
 	ctx->tm.pair_evaluations = 0;
 	ctx->tm.force_ms = 0;
 	ctx->kev_used = 0;
+	ctx->tev_used = 0;
 	CK(cudaEventRecord(ctx->ev_start, ctx->sc));
 	return NBODY_OK;
 }
@@ -1351,7 +1399,8 @@ static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double ta
 	// (3 nodes per stage: counter memset, K1, K2).  The reference's own 4-body run is pure
 	// launch latency (165 us/step in lab_5_N_body_CUDA/output/res_4body_float_64_.csv:2).
 	const bool graph_on = ctx->opt_use_graph > 0 || (ctx->opt_use_graph < 0 && ctx->n <= 16384);
-	if (graph_on && graph_key > 0 && ctx->world == 1 && !ctx->opt_time_kernels && n_steps >= 1) {
+	if (graph_on && graph_key > 0 && ctx->world == 1 && !ctx->opt_time_kernels && !ctx->opt_trace &&
+		n_steps >= 1) {
 		if (!ctx->graph || ctx->graph_scheme != graph_key || ctx->graph_tau != tau) {
 			if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
 			cudaGraph_t g = nullptr;
@@ -1560,6 +1609,26 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 		ctx->tm.variant = (ctx->opt_variant < 0 || ctx->opt_variant >= nv) ? 0u : (uint32_t)ctx->opt_variant;
 	}
 	*out = ctx->tm;
+	return NBODY_OK;
+}
+
+int nbody_get_trace(nbody_ctx* ctx, nbody_trace_entry* out, size_t cap, size_t* n_out) {
+	if (!ctx || !n_out || (!out && cap)) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	CK(cudaStreamSynchronize(ctx->sc));
+	CK(cudaStreamSynchronize(ctx->sm));
+	size_t k = 0;
+	for (; k < ctx->tev_used && k < cap; ++k) {
+		const nbody_ctx::TraceEv& t = ctx->tev[k];
+		float a = 0, d = 0;
+		CK(cudaEventElapsedTime(&a, ctx->ev_start, t.e0));
+		CK(cudaEventElapsedTime(&d, t.e0, t.e1));
+		out[k].kind = t.kind;
+		out[k].stream = t.stream;
+		out[k].start_ms = a;
+		out[k].dur_ms = d;
+	}
+	*n_out = ctx->tev_used;
 	return NBODY_OK;
 }
 

@@ -44,10 +44,26 @@ NB_HD unsigned sym_tile(unsigned nb, unsigned tpb, unsigned a, unsigned q, bool*
 	return b * tpb + (q - tpb) % tpb;
 }
 
-// tiles [t0,t1) of the walk that slice s of S takes
-NB_HD void sym_slice_range(unsigned ntiles, unsigned S, unsigned s, unsigned* t0, unsigned* t1) {
-	*t0 = (unsigned)(((unsigned long long)s * ntiles) / S);
-	*t1 = (unsigned)(((unsigned long long)(s + 1u) * ntiles) / S);
+// A walk is cut into S slices at STRIP granularity (a strip = 32 consecutive j-bodies of a tile, the
+// unit the kernel's warps consume): slice s takes strips [q0,q1) of the ntiles * spt strips of the
+// walk (spt = strips per tile).  Fine slices are what lets small problems fill the GPU.
+NB_HD void sym_slice_range(unsigned ntiles, unsigned spt, unsigned S, unsigned s, unsigned* q0,
+						   unsigned* q1) {
+	const unsigned long long nq = (unsigned long long)ntiles * spt;
+	*q0 = (unsigned)(((unsigned long long)s * nq) / S);
+	*q1 = (unsigned)(((unsigned long long)(s + 1u) * nq) / S);
+}
+// tiles [t0,t1) of the walk that the strip range [q0,q1) touches (t0 == t1 for an empty range)
+NB_HD void sym_slice_tiles(unsigned spt, unsigned q0, unsigned q1, unsigned* t0, unsigned* t1) {
+	*t0 = q0 / spt;
+	*t1 = q1 > q0 ? (q1 + spt - 1u) / spt : q0 / spt;
+}
+// bodies [lo,hi) of tile t (index in the walk) that belong to the strip range [q0,q1)
+NB_HD void sym_tile_part(unsigned t, unsigned spt, unsigned q0, unsigned q1, unsigned* lo,
+						 unsigned* hi) {
+	const unsigned first = t * spt, last = first + spt;
+	*lo = ((q0 > first ? q0 : first) - first) * 32u;
+	*hi = ((q1 < last ? q1 : last) - first) * 32u;
 }
 
 }  // namespace nbody

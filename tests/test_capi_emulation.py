@@ -475,3 +475,16 @@ def test_emulated_graph_is_not_replayed_across_uploads(oracle):
             got = ctx.download_aos()
             assert ctx.timing().uniform_mass == 1
             check_state(got, want, b, 1e-10)
+
+
+def test_emulated_trace_lists_every_operation_of_a_step():
+    """Option "trace": one entry per enqueued operation of the last call (per-rank launch list)."""
+    b = generators.uniform_bodies(700, seed=9)
+    with capi.Context(700, 64) as ctx:
+        ctx.set_option("trace", 1)
+        ctx.upload_aos(b)
+        ctx.step(capi.NBODY_RK4, 0.1, 1, sync=True)
+        tr = ctx.trace()
+    kinds = [t["kind"] for t in tr]
+    assert kinds.count("force") == 4 and kinds.count("stage") == 4 and kinds.count("memset") == 4
+    assert all(t["dur_ms"] >= 0 and t["stream"] == "compute" for t in tr)

@@ -60,8 +60,10 @@ extern "C" int sym_emulate_rhs(unsigned n, const double* bodies, double G, doubl
 
 	for (unsigned a = 0; a < nb; ++a)
 		for (unsigned slice = 0; slice < n_slices; ++slice) {
-			unsigned t0, t1;
-			sym_slice_range(sym_ntiles(nb, tpb, a), n_slices, slice, &t0, &t1);
+			unsigned q0, q1, t0, t1;
+			const unsigned spt = TJ / 32;
+			sym_slice_range(sym_ntiles(nb, tpb, a), spt, n_slices, slice, &q0, &q1);
+			sym_slice_tiles(spt, q0, q1, &t0, &t1);
 			// per-thread state of the CTA
 			std::vector<double> xi(block), yi(block), zi(block), mi(block), accm(3 * (size_t)block, 0.);
 			std::vector<unsigned> row(block);
@@ -77,11 +79,14 @@ extern "C" int sym_emulate_rhs(unsigned n, const double* bodies, double G, doubl
 				const unsigned jt = sym_tile(nb, tpb, a, t, &diag);
 				if (jt >= jt_total + tpb) return -2;  // outside the allocation
 				const unsigned j_first = jt * TJ;
-				const unsigned cnt = j_first >= n ? 0 : std::min(TJ, n - j_first);
+				unsigned cnt = j_first >= n ? 0 : std::min(TJ, n - j_first);
+				unsigned lo, hi;  // the bodies of this tile that belong to the unit's strips
+				sym_tile_part(t, spt, q0, q1, &lo, &hi);
+				cnt = std::min(cnt, hi);
 				const B4* tile = pos.data() + (size_t)jt * TJ;
 				if (diag) {
 					for (unsigned s = 0; s < block; ++s)
-						for (unsigned jj = 0; jj < cnt; ++jj) {
+						for (unsigned jj = lo; jj < cnt; ++jj) {
 							const double dx = xi[s] - tile[jj].x, dy = yi[s] - tile[jj].y, dz = zi[s] - tile[jj].z;
 							const double w = inv_cube(dx * dx + dy * dy + dz * dz) * (uniform_mass ? 1.0 : tile[jj].m);
 							accm[0 * block + s] += w * dx;
@@ -91,7 +96,7 @@ extern "C" int sym_emulate_rhs(unsigned n, const double* bodies, double G, doubl
 						}
 					continue;
 				}
-				for (unsigned s0 = 0; s0 < cnt; s0 += 32)
+				for (unsigned s0 = lo; s0 < cnt; s0 += 32)
 					for (unsigned warp = 0; warp < THREADS / 32; ++warp) {
 						// lane state: the travelling j-body, its accumulator and (for the check) its index
 						double jx[32], jy[32], jz[32], jm[32], ax[32], ay[32], az[32];
