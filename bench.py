@@ -49,7 +49,7 @@ def parse():
     ap.add_argument("--p2p", type=int, default=0,
                     help="1: peer-pull exchange (TMA reads of the peers' tiles) instead of NCCL all-gathers")
     ap.add_argument("--pair-symmetry", type=int, default=-1,
-                    help="-1: the library's automatic choice (pair-symmetric kernel for N >= 49152); "
+                    help="-1: the library's automatic choice (pair-symmetric kernel for N >= 2048); "
                          "1: evaluate each pair of distinct bodies once and credit both; "
                          "0: the one-sided kernel (every ordered pair, as the reference does; "
                          "bit-reproducible)")

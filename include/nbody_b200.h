@@ -114,7 +114,7 @@ int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab_5 #defines G (N_body.cu:30) */
 
 /* Named integer options: "time_kernels" (0/1), "slices" (0 = auto j-slices per launch),
- * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (-1 = auto: CUDA-graph replay of a step when n <= 16384 on one GPU; 0/1),
+ * "variant" (force-kernel variant id, -1 = auto, the default), "use_graph" (-1 = auto: CUDA-graph replay of a step when n <= 131072 on one GPU; 0/1),
  * "unimass" (-1 = at upload detect "all masses equal" and factor the mass out of the pair
  * sum, the default; 0 = never; set before the upload),
  * "pair_symmetry" (which force kernel runs.  0 = every ordered pair is evaluated separately, as
@@ -123,7 +123,7 @@ int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab
  * law) -- same per-pair bits, about half the arithmetic, 1.5x the throughput; both sides are
  * summed with floating-point atomics, so results are reproducible to ROUNDING only (same
  * tolerances against the reference); -1 = automatic, the default: the pair-symmetric kernel for
- * n >= 49152 unless the peer-pull exchange is connected, the one-sided kernel below that.
+ * n >= 2048 unless the peer-pull exchange is connected, the one-sided kernel below that.
  * On several GPUs the ranks split the blocks of one global schedule and the sums are
  * reduce-scattered (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose
  * block divides the per-rank block of nbody_partition, a forced variant that does not is

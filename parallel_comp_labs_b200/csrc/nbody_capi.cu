@@ -301,23 +301,27 @@ const Variant& variant_of(const nbody_ctx* c) {
 }
 
 // Pair-symmetric variant in use.  An explicit "sym_variant" wins; otherwise the first entry of a
-// preference list (measured on B200, profiles/r02_sym_sweep.md: N = 1M, G interactions/s) whose
-// block (threads * i-bodies) divides the per-rank block of the partition -- on several GPUs the
-// ranks must own whole blocks; the 256-row builds always fit.
-//   FP64 equal masses:   8 (I=8, re-read j) 1710 | 7 (I=6) 1708 | 5 (I=4, 5 CTAs/SM) 1696 | 3 (I=2) 1484
-//   FP64 general masses: 7 (I=6) 1522 | 5 1506 | 8 1493
-//   FP32:                1 (I=8, shuffled j) 3704 | 4 3437 | 0 3374 | 3 3254 | 2 (I=2) 3026
+// preference list whose block (threads * i-bodies) divides the per-rank block of the partition --
+// on several GPUs the ranks must own whole blocks; the 256-row builds always fit.  The lists are
+// measured (B200, G interactions/s; profiles/r02_sym_sweep.md at N = 1M, r02_sym_crossover.md below):
+//   FP64 equal masses   N = 1M: 8 (I=8, re-read j) 1710 | 7 (I=6) 1708 | 5 (I=4, 5 CTAs/SM) 1696 | 3 (I=2) 1484
+//                       N = 16k-64k: 5 >= 8;  N <= 8k: 3 (256-row blocks: more units) wins
+//   FP64 general masses N = 1M: 7 (I=6) 1522 | 5 1506 | 8 1493;  N <= 256k: 5 >= 7
+//   FP32                N >= 16k: 1 (I=8, shuffled j) | 3 (I=4, re-read j) | 2 (I=2);  N <= 12k: 3
+// On several GPUs the size that matters is the per-rank share of the pairs: n / sqrt(world).
 const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
 	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
 	long v = c->opt_sym_variant;
 	if (v >= 0 && v < nv) return tab[v];
-	static const int pref64_um[] = {8, 5, 3}, pref64_gen1[] = {7, 5, 3}, pref64_gen[] = {5, 8, 3},
-					 pref32[] = {1, 3, 2};
-	const int* pref = c->prec == 32 ? pref32
-					  : c->unimass	? pref64_um
-					  : c->world == 1 ? pref64_gen1
-									  : pref64_gen;
+	const double n_eff = (double)c->n / std::sqrt((double)c->world);
+	static const int p64_small[] = {3, 3, 3}, p64_mid[] = {5, 3, 3}, p64_um[] = {8, 5, 3},
+					 p64_gen[] = {7, 5, 3}, p32_small[] = {3, 2, 2}, p32[] = {1, 3, 2};
+	const int* pref;
+	if (c->prec == 32) pref = n_eff < 14000 ? p32_small : p32;
+	else if (n_eff < 10000) pref = p64_small;
+	else if (c->unimass) pref = n_eff < 120000 ? p64_mid : p64_um;
+	else pref = (n_eff < 500000 || c->world > 1) ? p64_mid : p64_gen;
 	for (int k = 0; k < 3; ++k) {
 		const SymVariant& sv = tab[pref[k]];
 		if (c->world == 1 || c->own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
@@ -326,10 +330,15 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 }
 
 // Which force kernel runs.  Option "pair_symmetry": 1 = the pair-symmetric kernel, 0 = the
-// default kernel (every ordered pair, bit-reproducible), -1 (default) = automatic: the
-// pair-symmetric kernel when the problem is large enough for its 256..1024-row blocks to fill the
-// GPU (measured crossover, profiles/r02_sym_crossover.md) and the exchange allows it.
-constexpr size_t SYM_AUTO_MIN_N = 49152;
+// one-sided kernel (every ordered pair, bit-reproducible), -1 (default) = automatic: the
+// pair-symmetric kernel from SYM_AUTO_MIN_N bodies on (with slices cut at strip granularity it
+// wins from ~2k bodies: profiles/r02_sym_crossover.md; below that a step is launch latency and
+// the one-sided kernel's ragged-tile loop is the shorter path) unless the peer-pull exchange is
+// connected.
+constexpr size_t SYM_AUTO_MIN_N = 2048;
+// CUDA-graph replay of a step (one GPU): while a step is shorter than ~10 ms the gaps between its
+// 3 operations per stage are worth removing (4 % of a step at N = 20k, r02_bench_uniform20k.json)
+constexpr size_t GRAPH_AUTO_MAX_N = 131072;
 bool sym_in_use(const nbody_ctx* c) {
 	if (c->opt_pair_symmetry == 0) return false;
 	if (c->opt_pair_symmetry > 0) return true;
@@ -555,7 +564,16 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 	return NBODY_OK;
 }
 
-// one pair-symmetric force launch over all bodies of `buf` (single GPU)
+// zero the ticket counter and the row-sum array of the pair-symmetric kernel
+int sym_prepare(nbody_ctx* ctx, const LaunchPlan& lp) {
+	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_MEMSET);
+	CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned), ctx->sc));
+	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
+	trace_end(ctx, ctx->sc, tr);
+	return NBODY_OK;
+}
+
+// one pair-symmetric force launch over all bodies of `buf`
 int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	const SymVariant& v = sym_variant_of(ctx);
 	SymParams p;
@@ -572,12 +590,8 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.counter = ctx->d_counters;
 	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
 	p.pos_rows = ctx->n_pad + SYM_EXTRA_TILES * PAD_UNIT;
-	{
-		const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_MEMSET);
-		CK(cudaMemsetAsync(p.counter, 0, sizeof(unsigned), ctx->sc));
-		CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
-		trace_end(ctx, ctx->sc, tr);
-	}
+	// (the ticket counter and the row sums were zeroed by sym_prepare, before the wait for the
+	// exchange, so that the memsets overlap the all-gather)
 	const unsigned long long units = (unsigned long long)lp.nb_own * lp.s_local;
 	const unsigned grid = (unsigned)std::min<unsigned long long>(units, lp.slots);
 	cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -664,13 +678,17 @@ int enqueue_forces(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, GatherMod
 	// as the reference's loop bounds do (struct_ode_system.hpp:64); pad bodies are not.
 	if (lp.sym) {
 		ctx->tm.pair_evaluations += ctx->sym_pairs;
+		// The walk of a block reaches half-way round the ring of blocks, so the whole stage array
+		// must be present before the launch: the exchange is waited for (tens of microseconds
+		// against a launch of milliseconds) instead of splitting the launch into local and remote
+		// tiles; the memsets of the launch go between "gather enqueued" and "gather awaited", so
+		// they overlap it.
+		if (ctx->world > 1 && mode == GATHER_NOW &&
+			(rc = enqueue_gather(ctx, buf_ptr(ctx, buf), ctx->e_g)))
+			return rc;
+		if ((rc = sym_prepare(ctx, lp))) return rc;
 		if (ctx->world > 1) {
-			// the walk of a block reaches half-way round the ring of blocks, so the whole stage
-			// array must be present: wait for the exchange (tens of microseconds against a launch
-			// of tens of milliseconds) instead of splitting the launch into local and remote tiles
-			int rc;
 			if (mode == GATHER_NOW) {
-				if ((rc = enqueue_gather(ctx, buf_ptr(ctx, buf), ctx->e_g))) return rc;
 				CK(cudaStreamWaitEvent(ctx->sc, ctx->e_g, 0));
 			} else if (mode == GATHER_PENDING_Y) {
 				CK(cudaStreamWaitEvent(ctx->sc, ctx->e_gy, 0));
@@ -1398,7 +1416,7 @@ static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double ta
 	// Launch-bound regime (small n, single rank): replay one captured step as a CUDA graph
 	// (3 nodes per stage: counter memset, K1, K2).  The reference's own 4-body run is pure
 	// launch latency (165 us/step in lab_5_N_body_CUDA/output/res_4body_float_64_.csv:2).
-	const bool graph_on = ctx->opt_use_graph > 0 || (ctx->opt_use_graph < 0 && ctx->n <= 16384);
+	const bool graph_on = ctx->opt_use_graph > 0 || (ctx->opt_use_graph < 0 && ctx->n <= GRAPH_AUTO_MAX_N);
 	if (graph_on && graph_key > 0 && ctx->world == 1 && !ctx->opt_time_kernels && !ctx->opt_trace &&
 		n_steps >= 1) {
 		if (!ctx->graph || ctx->graph_scheme != graph_key || ctx->graph_tau != tau) {

@@ -22,12 +22,13 @@ def _n_gpus():
 
 
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.parametrize("p2p,sym,port", [("0", "0", "29533"), ("1", "0", "29534")])
+@pytest.mark.parametrize("p2p,sym,port", [("0", "0", "29533"), ("1", "0", "29534"), ("0", "auto", "29536")])
 def test_two_ranks_match_oracle(p2p, sym, port):
     """p2p = 0: NCCL all-gather per stage; p2p = 1: peer-pull exchange (the force kernel's
     bulk-async copies read the other rank's tiles from its HBM; no collective per stage);
-    sym = 1 (the opt-in pair-symmetric kernel on two ranks) is exercised from
-    tests/test_zzz_gpu_pair_symmetry.py, which sorts last."""
+    sym = "0": the one-sided kernel, "auto": the library's choice (the pair-symmetric kernel at this
+    size: blocks of one global schedule split over the ranks, sums reduce-scattered); sym = "1" is
+    also exercised from tests/test_zzz_gpu_pair_symmetry.py, which sorts last."""
     env = dict(os.environ, NBODY_P2P=p2p, NBODY_PAIR_SYM=sym)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
                         "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",

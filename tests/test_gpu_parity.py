@@ -15,19 +15,23 @@ pytestmark = pytest.mark.gpu
 TOL64_RHS, TOL64_TRAJ, TOL32 = 1e-12, 1e-10, 1e-4
 
 
-def gpu_rhs(bodies, prec=64, eps=1e-6, G=6.67e-11, variant=-1, slices=0):
+def gpu_rhs(bodies, prec=64, eps=1e-6, G=6.67e-11, variant=-1, slices=0, sym=-1):
+    """sym = -1: the library's automatic choice of force kernel (pair-symmetric from 2048 bodies
+    on), 0: the one-sided kernel (what `variant` selects builds of), 1: the pair-symmetric one."""
     with capi.Context(bodies.shape[0], prec) as ctx:
         ctx.set_params(G, eps)
         ctx.set_option("variant", variant)
         ctx.set_option("slices", slices)
+        ctx.set_option("pair_symmetry", 0 if (variant >= 0 or slices) and sym < 0 else sym)
         ctx.upload_aos(bodies)
         return ctx.rhs().astype(np.float64)
 
 
-def gpu_run(bodies, scheme, tau, steps, prec=64, eps=1e-6, G=6.67e-11, graph=0):
+def gpu_run(bodies, scheme, tau, steps, prec=64, eps=1e-6, G=6.67e-11, graph=0, sym=-1):
     with capi.Context(bodies.shape[0], prec) as ctx:
         ctx.set_params(G, eps)
         ctx.set_option("use_graph", graph)
+        ctx.set_option("pair_symmetry", sym)
         ctx.upload_aos(bodies)
         ctx.step(scheme, tau, steps, sync=True)
         return ctx.download_aos().astype(np.float64)
@@ -301,10 +305,16 @@ def test_uniform_mass_specialisation(oracle):
 
 
 def test_determinism():
+    """pair_symmetry = 0 (the one-sided kernel) is bit-reproducible run to run: dynamic unit
+    scheduling, but fixed-order slice reduction.  The automatic choice at this size is the
+    pair-symmetric kernel, whose sums go through floating-point atomics: reproducible to rounding."""
     b = generators.plummer_bodies(5000, seed=2)
-    a = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
-    c = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
-    assert np.array_equal(a, c)      # dynamic unit scheduling, fixed-order slice reduction
+    a = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3, sym=0)
+    c = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3, sym=0)
+    assert np.array_equal(a, c)
+    d = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
+    e = gpu_run(b, capi.NBODY_RK4, 1e-3, 2, eps=1e-3)
+    assert rel_inf(d[:, 1:], e[:, 1:]) < 1e-13 and rel_inf(d[:, 1:], a[:, 1:]) < 1e-12
 
 
 # ------------------------------------------------------------------ FP32
