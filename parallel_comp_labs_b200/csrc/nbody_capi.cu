@@ -456,7 +456,8 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 		if (per_sm < 1) return fail(ctx, NBODY_ERR_CUDA, "force kernel does not fit on an SM");
 		lp->slots = (unsigned)per_sm * (unsigned)ctx->n_sm;
 		// shortest walk of a block: tpb * (1 + h) tiles with h >= (nb-1)/2 - (nb even ? 0 : 0)
-		const unsigned min_walk = sym_ntiles(lp->nb, lp->tpb, lp->nb - 1);
+		const unsigned h_min = (lp->nb & 1u) ? (lp->nb - 1u) / 2u : lp->nb / 2u - 1u;
+		const unsigned min_walk = lp->tpb * (1u + h_min);
 		// slices are cut at strip granularity (32 j-bodies; sym_schedule.h), at least 2 strips each
 		lp->s_local = choose_slices(lp->nb_own, min_walk * (TJ / 32), lp->slots, ctx->opt_slices,
 									MAX_SYM_SLICES);

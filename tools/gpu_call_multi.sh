@@ -19,7 +19,7 @@ fi
 for sym in auto 0; do
 	NBODY_PAIR_SYM=$sym step multi_check_sym_$sym 600 $TR --master-port 29541 tests/tools/multi_check.py 6000
 done
-NBODY_P2P=1 step multi_check_p2p 600 $TR --master-port 29542 tests/tools/multi_check.py 6000
+[ "$G" -le 4 ] && NBODY_P2P=1 step multi_check_p2p 600 $TR --master-port 29542 tests/tools/multi_check.py 6000
 bench_line bench_1m 29551 600 --steps 5 --warmup 3 --trace-out "$OUT/trace_1m.json"
 bench_line bench_256k 29552 400 --bodies 262144 --steps 5 --warmup 3 --trace-out "$OUT/trace_256k.json"
 bench_line bench_1m_fp32 29553 400 --precision 32 --steps 5 --warmup 3
