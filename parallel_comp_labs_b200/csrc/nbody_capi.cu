@@ -353,13 +353,25 @@ bool sym_in_use(const nbody_ctx* c) {
 // 1111 / 1113 G int/s, i.e. the half-unit tail model; 100 units per CTA (29 slices there) keeps
 // the tail at 0.5 % for 0.9 GB of partial sums per launch (0.1 % of the launch's HBM time).
 unsigned choose_slices(unsigned n_itiles, unsigned jt_count, unsigned slots, long forced,
-					   unsigned max_slices = MAX_SLICES) {
-	const unsigned UNITS_PER_SLOT = 100, MIN_TILES = 2;
+					   unsigned max_slices = MAX_SLICES, unsigned units_per_slot = 100) {
+	const unsigned MIN_TILES = 2;
 	unsigned smax = std::min<unsigned>(max_slices, std::max(1u, jt_count / MIN_TILES));
 	if (forced > 0) return std::min<unsigned>((unsigned)forced, std::max(1u, jt_count));
 	if (n_itiles == 0) return 1;
-	unsigned want = (UNITS_PER_SLOT * slots + n_itiles - 1) / n_itiles;
+	unsigned want = (units_per_slot * slots + n_itiles - 1) / n_itiles;
 	return std::max(1u, std::min(want, smax));
+}
+
+// Units per resident CTA for the pair-symmetric kernel.  A unit costs a fixed o ~ 2 us (i-bodies
+// loaded, shared sums zeroed, 3 * BLOCK REDs at its end) and the launch ends with a tail of about
+// half a unit, so with T = the launch's time per CTA slot the loss o * U / T + 1 / (2 U) is
+// smallest at U = sqrt(T / (2 o)).  (Measured: 256k bodies on 8 GPUs, T = 5 ms: U = 100 units of
+// 52 us lost 4.3 % against the one-GPU rate; the formula gives U = 35.)
+unsigned sym_units_per_slot(double pair_evaluations, unsigned prec) {
+	const double rate = prec == 64 ? 0.85e12 : 1.8e12;	// pair evaluations / s of one B200
+	const double t_us = pair_evaluations / rate * 1e6;
+	const double u = std::sqrt(t_us / 4.0);
+	return (unsigned)std::max(4.0, std::min(400.0, u));
 }
 }  // namespace
 
@@ -459,14 +471,14 @@ int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 		const unsigned h_min = (lp->nb & 1u) ? (lp->nb - 1u) / 2u : lp->nb / 2u - 1u;
 		const unsigned min_walk = lp->tpb * (1u + h_min);
 		// slices are cut at strip granularity (32 j-bodies; sym_schedule.h), at least 2 strips each
-		lp->s_local = choose_slices(lp->nb_own, min_walk * (TJ / 32), lp->slots, ctx->opt_slices,
-									MAX_SYM_SLICES);
-		lp->s_remote = 0;
 		const int key = (int)(sv.threads * sv.ipt);
 		if (ctx->sym_pairs_key != key) {
 			ctx->sym_pairs = sym_pair_evaluations((unsigned)ctx->n, lp->nb, lp->tpb, lp->block0, lp->nb_own);
 			ctx->sym_pairs_key = key;
 		}
+		lp->s_local = choose_slices(lp->nb_own, min_walk * (TJ / 32), lp->slots, ctx->opt_slices,
+									MAX_SYM_SLICES, sym_units_per_slot((double)ctx->sym_pairs, ctx->prec));
+		lp->s_remote = 0;
 		return NBODY_OK;
 	}
 	lp->nb = lp->tpb = lp->rows_pad = lp->block0 = lp->nb_own = 0;
