@@ -465,8 +465,12 @@ def run_b200(args):
             "roofline": {
                 "bound": "fp64_fma_pipe" if args.precision == 64 else "fp32_fma_pipe",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": (None if tm.pair_symmetry else
-                            TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision))),
+                "traffic": TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision,
+                                                         bool(tm.pair_symmetry))),
+                "algorithmic_bytes_per_launch": int(n * 4 * np.dtype(dtype).itemsize
+                                                    + (e - b) * 3 * np.dtype(dtype).itemsize),
+                "pipe_util_ncu": PIPE_UTIL_NCU.get((args.precision, bool(tm.pair_symmetry),
+                                                    bool(tm.uniform_mass))),
                 "kernel": "nbody::force_sym_kernel" if tm.pair_symmetry else "nbody::force_kernel",
                 "mean_launch_ms": mean_force_ms,
                 "evaluated_pairs_per_delivered_interaction":
@@ -504,8 +508,24 @@ def run_b200(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
 # `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
+# Key: (n, gpus, precision, pair-symmetric kernel?)
 TRAFFIC_BYTES_PER_LAUNCH = {
-    (1 << 20, 1, 64): 83091968 + 963913216,   # profiles/r01_force_kernel_1M_ncu_full.csv
+    (1 << 20, 1, 64, False): 83091968 + 963913216,   # profiles/r01_force_kernel_1M_ncu_full.csv
+    (1 << 18, 1, 64, True): 14749184 + 11520,        # profiles/r02_ncu_k1s_fp64_equal_262144.csv
+    (1 << 18, 1, 32, True): 7392768 + 0,             # profiles/r02_ncu_k1s_fp32_262144.csv
+}
+
+# FMA-pipe utilisation of the dominant kernel from the committed ncu captures
+# (sm__inst_executed_pipe_fp64 / sm__inst_executed_pipe_fma .avg.pct_of_peak_sustained_active);
+# key: (precision, pair-symmetric kernel?, equal masses?)
+PIPE_UTIL_NCU = {
+    (64, True, True): {"value": 0.8313, "source": "profiles/r02_ncu_k1s_fp64_equal_262144.csv"},
+    (64, True, False): {"value": 0.8248, "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv"},
+    (32, True, True): {"value": 0.6923, "source": "profiles/r02_ncu_k1s_fp32_262144.csv",
+                       "note": "issue-bound: 83 % of issue slots"},
+    (64, False, True): {"value": 0.8974, "source": "profiles/r01_force_kernel_1M_ncu_full.csv"},
+    (64, False, False): {"value": 0.8195, "source": "profiles/r02_ncu_k1_fp64_general_20000.csv (N = 20k)"},
+    (32, False, True): {"value": 0.7031, "source": "profiles/r02_ncu_k1_fp32_131072.csv"},
 }
 
 

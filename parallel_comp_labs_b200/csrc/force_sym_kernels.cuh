@@ -86,7 +86,16 @@ struct SymParams {
 // One j-body (travelling with its accumulator) against the I i-bodies of this thread.
 // UM: all masses equal and factored out (applied once in K2); else m_j weights the action on i
 // and m_i the reaction on j.
-template <typename T, int I, int ORD, bool UM, bool EXACT>
+__device__ __forceinline__ double sym_mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double sym_add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float sym_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float sym_add(float a, float b) { return __fadd_rn(a, b); }
+
+// ACC = 0: both sides accumulate with FMA (a += w d; 6 instructions with three register operands);
+// ACC = 1: f = w d once (3 multiplies), then a_i += f, a_j -= f (6 adds): 9 two-operand instructions
+// instead of 6 three-operand ones -- an experiment on the register-file-cycle model of DESIGN.md 4
+// (one more rounding per term; same tolerances).
+template <typename T, int I, int ORD, bool UM, bool EXACT, int ACC = 0>
 __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz, const T jm,
 											  const T (&xi)[I], const T (&yi)[I], const T (&zi)[I],
 											  const T (&mi)[I], Acc<T, I>& a, T& ajx, T& ajy, T& ajz,
@@ -103,12 +112,19 @@ __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz,
 		const T w = inv_cube_m<ORD, true>(r2, T(1));  // max(r2,eps2)^{-3/2}
 		const T wi = UM ? w : w * jm;
 		const T wj = UM ? w : w * mi[k];
-		a.x[k] = fma(wi, dx, a.x[k]);
-		a.y[k] = fma(wi, dy, a.y[k]);
-		a.z[k] = fma(wi, dz, a.z[k]);
-		ajx = fma(-wj, dx, ajx);  // force on j = -(force on i) per unit of the other's mass
-		ajy = fma(-wj, dy, ajy);
-		ajz = fma(-wj, dz, ajz);
+		if (ACC == 1 && UM) {
+			// explicit roundings: the compiler must not contract these back into FMAs
+			const T fx = sym_mul(w, dx), fy = sym_mul(w, dy), fz = sym_mul(w, dz);
+			a.x[k] = sym_add(a.x[k], fx); a.y[k] = sym_add(a.y[k], fy); a.z[k] = sym_add(a.z[k], fz);
+			ajx = sym_add(ajx, -fx); ajy = sym_add(ajy, -fy); ajz = sym_add(ajz, -fz);
+		} else {
+			a.x[k] = fma(wi, dx, a.x[k]);
+			a.y[k] = fma(wi, dy, a.y[k]);
+			a.z[k] = fma(wi, dz, a.z[k]);
+			ajx = fma(-wj, dx, ajx);  // force on j = -(force on i) per unit of the other's mass
+			ajy = fma(-wj, dy, ajy);
+			ajz = fma(-wj, dz, ajz);
+		}
 	}
 	if (!EXACT) {
 #pragma unroll
@@ -123,7 +139,7 @@ __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz,
 // read in the loop).  ROT = 1: only the accumulator travels; lane l re-reads the j-body that is
 // visiting it, strip[(l + r + 1) & 31], from the staged tile (distinct consecutive addresses:
 // conflict-free; 2 LDS instead of 6 SHFL per step).  Same arithmetic, same bits.
-template <typename T, int I, int ORD, bool UM, bool EXACT, bool ROT>
+template <typename T, int I, int ORD, bool UM, bool EXACT, bool ROT, int ACC = 0>
 __device__ __forceinline__ void sym_strip(const typename V4<T>::type* strip, const int lane,
 										   const T (&xi)[I],
 										   const T (&yi)[I], const T (&zi)[I], const T (&mi)[I],
@@ -137,7 +153,7 @@ __device__ __forceinline__ void sym_strip(const typename V4<T>::type* strip, con
 	mn = 0x7fffffff;
 #pragma unroll 2
 	for (int r = 0; r < 32; ++r) {
-		interact_sym<T, I, ORD, UM, EXACT>(jx, jy, jz, jm, xi, yi, zi, mi, loc, ajx, ajy, ajz, cl, mn);
+		interact_sym<T, I, ORD, UM, EXACT, ACC>(jx, jy, jz, jm, xi, yi, zi, mi, loc, ajx, ajy, ajz, cl, mn);
 		// pass the j-body and its accumulator on; after 32 passes they are home again
 		if (ROT) {
 			const typename V4<T>::type q = strip[(lane + r + 1) & 31];
@@ -161,7 +177,7 @@ constexpr size_t force_sym_smem_bytes() {
 		   (size_t)3 * I * THREADS * sizeof(T) + STAGES * sizeof(uint64_t) + 16;
 }
 
-template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int ORD, int ROT = 0>
+template <typename T, int THREADS, int I, int STAGES, int MINB, int UM, int ORD, int ROT = 0, int ACC = 0>
 __global__ void __launch_bounds__(THREADS, MINB)
 	force_sym_kernel(const SymParams p, const Clamp<T> cl) {
 	typedef typename V4<T>::type vec4;
@@ -271,12 +287,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
 			} else {
 				for (int s0 = lo; s0 < cnt; s0 += 32) {	// strips that hold a real body
 					T ajx, ajy, ajz;
-					sym_strip<T, I, ORD, UM != 0, false, ROT != 0>(tile + s0, tid & 31, xi, yi, zi, mi,
-																   loc, ajx, ajy, ajz, cl, mn, next_lane);
+					sym_strip<T, I, ORD, UM != 0, false, ROT != 0, ACC>(tile + s0, tid & 31, xi, yi, zi, mi,
+																		loc, ajx, ajy, ajz, cl, mn, next_lane);
 					if (__any_sync(0xffffffffu, mn <= cl.thresh))  // rare: redo the strip exactly
-						sym_strip<T, I, ORD, UM != 0, true, ROT != 0>(tile + s0, tid & 31, xi, yi, zi,
-																	  mi, loc, ajx, ajy, ajz, cl, mn,
-																	  next_lane);
+						sym_strip<T, I, ORD, UM != 0, true, ROT != 0, ACC>(tile + s0, tid & 31, xi, yi, zi,
+																		   mi, loc, ajx, ajy, ajz, cl, mn,
+																		   next_lane);
 					const unsigned j = j_first + (unsigned)s0 + (unsigned)(tid & 31);
 					NB_CHECK(j < p.rows_pad);
 					atomicAdd(gjx + j, ajx);  // result unused -> RED.ADD

@@ -135,18 +135,19 @@ struct SymVariant {
 	void (*launch[2])(dim3, cudaStream_t, size_t, const SymParams&, double eps2);
 	const char* name;
 };
-template <typename T, int TH, int I, int ST, int MB, int UM, int ORD, int ROT>
+template <typename T, int TH, int I, int ST, int MB, int UM, int ORD, int ROT, int ACC>
 void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p, double eps2) {
-	auto kern = force_sym_kernel<T, TH, I, ST, MB, UM, ORD, ROT>;
+	auto kern = force_sym_kernel<T, TH, I, ST, MB, UM, ORD, ROT, ACC>;
 	NB_LAUNCH(kern, grid, dim3(TH), smem, s, p, make_clamp<T>(eps2));
 }
-#define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT)                                             \
+#define NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, ACC)                                      \
 	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
-				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT>,                 \
-				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT>},                \
-				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT>,                              \
-				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT>},                             \
-				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT }
+				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,            \
+				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},           \
+				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                         \
+				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                        \
+				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT "/acc" #ACC }
+#define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT) NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, 0)
 // {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order, rot}
 // rot = 0: the j-body is shuffled round the warp with its accumulator; rot = 1: it is re-read
 // from the staged tile and only the accumulator is shuffled (force_sym_kernels.cuh, sym_strip).
@@ -161,6 +162,10 @@ const SymVariant g_sym64[] = {
 	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2, 1),
+	// experiment (equal masses only): f = w d, then a_i += f, a_j -= f instead of two FMAs per component
+	NB_SYM_VARIANT_A(double, 128, 8, 2, 3, 2, 1, 1),  // 9
+	NB_SYM_VARIANT_A(double, 128, 4, 2, 5, 2, 1, 1),  // 10
+	NB_SYM_VARIANT_A(double, 128, 6, 2, 4, 2, 1, 1),  // 11
 };
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),
