@@ -511,6 +511,7 @@ def run_b200(args):
 # Key: (n, gpus, precision, pair-symmetric kernel?)
 TRAFFIC_BYTES_PER_LAUNCH = {
     (1 << 20, 1, 64, False): 83091968 + 963913216,   # profiles/r01_force_kernel_1M_ncu_full.csv
+    (1 << 20, 1, 64, True): 58879744 + 550656,       # profiles/r02_ncu_k1s_fp64_equal_1M.csv
     (1 << 18, 1, 64, True): 14749184 + 11520,        # profiles/r02_ncu_k1s_fp64_equal_262144.csv
     (1 << 18, 1, 32, True): 7392768 + 0,             # profiles/r02_ncu_k1s_fp32_262144.csv
 }
@@ -519,7 +520,7 @@ TRAFFIC_BYTES_PER_LAUNCH = {
 # (sm__inst_executed_pipe_fp64 / sm__inst_executed_pipe_fma .avg.pct_of_peak_sustained_active);
 # key: (precision, pair-symmetric kernel?, equal masses?)
 PIPE_UTIL_NCU = {
-    (64, True, True): {"value": 0.8313, "source": "profiles/r02_ncu_k1s_fp64_equal_262144.csv"},
+    (64, True, True): {"value": 0.8377, "source": "profiles/r02_ncu_k1s_fp64_equal_1M.csv"},
     (64, True, False): {"value": 0.8248, "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv"},
     (32, True, True): {"value": 0.6923, "source": "profiles/r02_ncu_k1s_fp32_262144.csv",
                        "note": "issue-bound: 83 % of issue slots"},

@@ -91,10 +91,13 @@ __device__ __forceinline__ double sym_add(double a, double b) { return __dadd_rn
 __device__ __forceinline__ float sym_mul(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float sym_add(float a, float b) { return __fadd_rn(a, b); }
 
-// ACC = 0: both sides accumulate with FMA (a += w d; 6 instructions with three register operands);
+// ACC = 0 (every shipped build): both sides accumulate with FMA (a += w d).
 // ACC = 1: f = w d once (3 multiplies), then a_i += f, a_j -= f (6 adds): 9 two-operand instructions
-// instead of 6 three-operand ones -- an experiment on the register-file-cycle model of DESIGN.md 4
-// (one more rounding per term; same tolerances).
+// instead of 6 three-operand FMAs.  Built and measured in round 2 to test whether the FMAs' third
+// register operand is what costs the FP64 pipe its last 17 %: it is not -- 21 instructions per
+// evaluation ran at 2.26 cycles each (1565 vs 1718 G int/s, profiles/r02_experiment_acc_muladd.jsonl),
+// the 18-instruction build at 2.40: the pipe delivers ~84-88 % for this instruction stream either
+// way.  The template parameter stays for the record; no variant table entry uses it.
 template <typename T, int I, int ORD, bool UM, bool EXACT, int ACC = 0>
 __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz, const T jm,
 											  const T (&xi)[I], const T (&yi)[I], const T (&zi)[I],

@@ -162,10 +162,6 @@ const SymVariant g_sym64[] = {
 	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2, 1),
-	// experiment (equal masses only): f = w d, then a_i += f, a_j -= f instead of two FMAs per component
-	NB_SYM_VARIANT_A(double, 128, 8, 2, 3, 2, 1, 1),  // 9
-	NB_SYM_VARIANT_A(double, 128, 4, 2, 5, 2, 1, 1),  // 10
-	NB_SYM_VARIANT_A(double, 128, 6, 2, 4, 2, 1, 1),  // 11
 };
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),

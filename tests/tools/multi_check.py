@@ -9,7 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
-from parallel_comp_labs_b200 import capi, generators
+from parallel_comp_labs_b200 import capi, generators, tableaux
 from oracle import Oracle
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -68,7 +68,20 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
                     own = ctx.download_aos_owned().astype(np.float64)
                     res[f"rk{scheme}_owned"] = (float(np.abs(own - fin[b:e]).max()
                                                       / np.abs(fin[:, 1:]).max()) if e > b else 0.0)
-            lim = {"rhs": tol, "_r": tol, "_dv": max(tol * 10, dv_floor), "_snap": 0.0 if prec == 64 else 1e-6,
+            if prec == 64 and not P2P:
+                # K2g on several ranks: one embedded DOPRI5 step (error norms all-reduced with MAX),
+                # reject it (undo), take a smaller one -- against the oracle's generic integrator
+                tb = tableaux.TABLEAUX["dopri5"]
+                ctx.upload_aos(bodies)
+                nrm = ctx.step_embedded(tb["a"], tb["b"], tb["b_err"], 2 * tau)
+                w1, werr = o.rk_general(bodies, tb["a"], tb["b"], 2 * tau, 1, b_err=tb["b_err"], eps=eps, threads=4)
+                res["emb_norms"] = float(np.abs(nrm / werr - 1).max())   # each of the 4 norms, relative
+                ctx.step_undo()
+                ctx.step_embedded(tb["a"], tb["b"], tb["b_err"], tau)
+                fin = ctx.download_aos().astype(np.float64)
+                w2, _ = o.rk_general(bodies, tb["a"], tb["b"], tau, 1, eps=eps, threads=4)
+                res["emb_r"] = float(np.abs(fin[:, 1:4] - w2[:, 1:4]).max() / np.abs(w2[:, 1:4]).max())
+            lim = {"rhs": tol, "_r": tol, "_dv": max(tol * 10, dv_floor), "emb_norms": 1e-4, "_snap": 0.0 if prec == 64 else 1e-6,
                    "_E": max(tol * 10, 1e-9), "_owned": tol if PAIR_SYM else 0.0}
             good = all(v <= next(l for suf, l in lim.items() if k_.endswith(suf))
                        for k_, v in res.items() if k_ != "sym")
