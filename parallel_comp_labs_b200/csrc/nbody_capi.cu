@@ -142,10 +142,10 @@ void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p
 }
 #define NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, ACC)                                      \
 	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
-				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,            \
-				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},           \
-				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                         \
-				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                        \
+				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,       \
+				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},      \
+				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                    \
+				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                   \
 				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT "/acc" #ACC }
 #define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT) NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, 0)
 // {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order, rot}
@@ -162,6 +162,10 @@ const SymVariant g_sym64[] = {
 	NB_SYM_VARIANT(double, 128, 4, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 6, 2, 4, 2, 1),
 	NB_SYM_VARIANT(double, 128, 8, 2, 3, 2, 1),
+	// 64-thread CTAs: the same 3 warps per scheduler as entry 8 in blocks half the size, which
+	// halves the partition and tail granularity (profiles/r02_sym_sweep2.md)
+	NB_SYM_VARIANT(double, 64, 8, 2, 6, 2, 1),	 // 9: 512-row blocks
+	NB_SYM_VARIANT(double, 64, 4, 2, 10, 2, 1),	 // 10: 256-row blocks
 };
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),
@@ -169,6 +173,7 @@ const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 2, 2, 8, 2, 0),
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 1),
 	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 1),
+	NB_SYM_VARIANT(float, 64, 8, 2, 10, 2, 1),	// 5: 64-thread CTAs, 512-row blocks
 };
 constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
 constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);
@@ -304,11 +309,12 @@ const Variant& variant_of(const nbody_ctx* c) {
 // Pair-symmetric variant in use.  An explicit "sym_variant" wins; otherwise the first entry of a
 // preference list whose block (threads * i-bodies) divides the per-rank block of the partition --
 // on several GPUs the ranks must own whole blocks; the 256-row builds always fit.  The lists are
-// measured (B200, G interactions/s; profiles/r02_sym_sweep.md at N = 1M, r02_sym_crossover.md below):
-//   FP64 equal masses   N = 1M: 8 (I=8, re-read j) 1710 | 7 (I=6) 1708 | 5 (I=4, 5 CTAs/SM) 1696 | 3 (I=2) 1484
-//                       N = 16k-64k: 5 >= 8;  N <= 8k: 3 (256-row blocks: more units) wins
-//   FP64 general masses N = 1M: 7 (I=6) 1522 | 5 1506 | 8 1493;  N <= 256k: 5 >= 7
-//   FP32                N >= 16k: 1 (I=8, shuffled j) | 3 (I=4, re-read j) | 2 (I=2);  N <= 12k: 3
+// measured (B200, G interactions/s; profiles/r02_sym_sweep.md, r02_sym_sweep2.md at N = 1M,
+// r02_sym_crossover.md and r02_sym_sweep3.md per size):
+//   FP64 equal masses   N = 1M: 9 (64 threads, I=8) 1722 | 8 (128 threads, I=8) 1720 | 7 (I=6) 1720 | 5 (I=4) 1676
+//                       N = 32k-256k: 9 ahead by 0.4-2 %;  N = 16k-20k: 5;  N <= 8k: 3 (256-row blocks)
+//   FP64 general masses N >= 512k: 7 1529 | 9 1525 | 5 1518 | 8 1472;  N = 64k-256k: 9 >= 5 >= 7;  below: 5
+//   FP32 equal masses   N >= 16k: 1 (I=8, shuffled j);  general masses: 5 (64 threads, I=8, re-read j);  N <= 12k: 3
 // On several GPUs the size that matters is the per-rank share of the pairs: n / sqrt(world).
 const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
@@ -316,13 +322,15 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	long v = c->opt_sym_variant;
 	if (v >= 0 && v < nv) return tab[v];
 	const double n_eff = (double)c->n / std::sqrt((double)c->world);
-	static const int p64_small[] = {3, 3, 3}, p64_mid[] = {5, 3, 3}, p64_um[] = {8, 5, 3},
-					 p64_gen[] = {7, 5, 3}, p32_small[] = {3, 2, 2}, p32[] = {1, 3, 2};
+	// per-size winners of profiles/r02_sym_crossover.md and r02_sym_sweep3.md
+	static const int p64_small[] = {3, 3, 3}, p64_mid[] = {5, 3, 3}, p64_fine[] = {9, 5, 3},
+					 p64_um[] = {8, 9, 5}, p64_gen[] = {7, 9, 5}, p32_small[] = {3, 2, 2},
+					 p32_um[] = {1, 3, 2}, p32_gen[] = {5, 3, 2};
 	const int* pref;
-	if (c->prec == 32) pref = n_eff < 14000 ? p32_small : p32;
+	if (c->prec == 32) pref = n_eff < 14000 ? p32_small : c->unimass ? p32_um : p32_gen;
 	else if (n_eff < 10000) pref = p64_small;
-	else if (c->unimass) pref = n_eff < 120000 ? p64_mid : p64_um;
-	else pref = (n_eff < 500000 || c->world > 1) ? p64_mid : p64_gen;
+	else if (c->unimass) pref = n_eff < 26000 ? p64_mid : n_eff < 400000 ? p64_fine : p64_um;
+	else pref = n_eff < 50000 ? p64_mid : (n_eff < 500000 || c->world > 1) ? p64_fine : p64_gen;
 	for (int k = 0; k < 3; ++k) {
 		const SymVariant& sv = tab[pref[k]];
 		if (c->world == 1 || c->own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
