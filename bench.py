@@ -520,10 +520,12 @@ TRAFFIC_BYTES_PER_LAUNCH = {
 # (sm__inst_executed_pipe_fp64 / sm__inst_executed_pipe_fma .avg.pct_of_peak_sustained_active);
 # key: (precision, pair-symmetric kernel?, equal masses?)
 PIPE_UTIL_NCU = {
-    (64, True, True): {"value": 0.8377, "source": "profiles/r02_ncu_k1s_fp64_equal_1M.csv"},
-    (64, True, False): {"value": 0.8248, "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv"},
+    (64, True, True): {"value": 0.8377, "source": "profiles/r02_ncu_k1s_fp64_equal_1M.csv",
+                       "captured_sym_variant": 8},
+    (64, True, False): {"value": 0.8248, "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv",
+                        "captured_sym_variant": 5},
     (32, True, True): {"value": 0.6923, "source": "profiles/r02_ncu_k1s_fp32_262144.csv",
-                       "note": "issue-bound: 83 % of issue slots"},
+                       "captured_sym_variant": 1, "note": "issue-bound: 83 % of issue slots"},
     (64, False, True): {"value": 0.8974, "source": "profiles/r01_force_kernel_1M_ncu_full.csv"},
     (64, False, False): {"value": 0.8195, "source": "profiles/r02_ncu_k1_fp64_general_20000.csv (N = 20k)"},
     (32, False, True): {"value": 0.7031, "source": "profiles/r02_ncu_k1_fp32_131072.csv"},

@@ -142,10 +142,10 @@ void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p
 }
 #define NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, ACC)                                      \
 	SymVariant { TH, I, force_sym_smem_bytes<T, TH, I, ST>(),                                  \
-				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,       \
-				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},      \
-				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                    \
-				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                   \
+				 {(const void*)force_sym_kernel<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,            \
+				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},           \
+				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                         \
+				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                        \
 				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT "/acc" #ACC }
 #define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT) NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, 0)
 // {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order, rot}
