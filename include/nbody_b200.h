@@ -55,6 +55,10 @@ typedef struct nbody_timing {
 									option "pair_symmetry" (each evaluation serves both bodies) */
 	uint32_t pair_symmetry;		 /* 1 if the pair-symmetric kernels are in use */
 	uint32_t sym_variant;		 /* pair-symmetric kernel variant index in use (0 if not in use) */
+	uint64_t graph_captures;	 /* steps captured into a CUDA graph since create: a replayed step
+									(option "use_graph") is captured once per scheme, tau and mass
+									state, and again only after an option, parameter or upload
+									changed what the capture holds by value */
 } nbody_timing;
 
 /* Option "trace" = 1: every operation a call enqueues (force launch, fused stage kernel, memsets,

@@ -254,6 +254,7 @@ struct nbody_ctx {
 	std::string err;
 	// cached CUDA graph of one step
 	cudaGraphExec_t graph = nullptr;
+	uint64_t graph_captures = 0;
 	int graph_scheme = 0;
 	double graph_tau = 0;
 };
@@ -1235,6 +1236,20 @@ int nbody_owned_range(const nbody_ctx* ctx, size_t* begin, size_t* end) {
 	return NBODY_OK;
 }
 
+// The one thing an upload can change that a captured step has baked into its kernel parameters by
+// value: which kernels run (equal masses or not) and the common mass (K2's mass_scale).  The cached
+// graph survives an upload that leaves both alone -- the end-to-end loop that re-uploads a state
+// every step would otherwise re-capture and re-instantiate it each time -- and is dropped otherwise.
+static void set_uniform_mass(nbody_ctx* ctx, bool uni, double m0) {
+	const double um = uni ? m0 : 0.;
+	if (ctx->graph && (uni != ctx->unimass || um != ctx->uniform_mass)) {
+		cudaGraphExecDestroy(ctx->graph);
+		ctx->graph = nullptr;
+	}
+	ctx->unimass = uni;
+	ctx->uniform_mass = um;
+}
+
 // Every body has the same mass (e.g. the Plummer configs, the 4-body test)?  Then the mass is
 // factored out of the pair sum.  `stride` = elements between consecutive masses.
 static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t stride) {
@@ -1250,17 +1265,13 @@ static void detect_uniform_mass(nbody_ctx* ctx, const void* masses, size_t strid
 		for (size_t i = 1; uni && i < ctx->n; ++i) uni = p[i * stride] == p[0];
 	}
 	uni = uni && std::isfinite(m0);
-	if (uni != ctx->unimass && ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
-	ctx->unimass = uni;
-	ctx->uniform_mass = uni ? m0 : 0.;
+	set_uniform_mass(ctx, uni, m0);
 }
 
 static int upload_common(nbody_ctx* ctx) {
 	ctx->undo_valid = false;
 	ctx->k0_slot = -1;
-	// a captured step bakes kernel parameters in by value (the uniform mass among them): never
-	// replay a graph across an upload
-	if (ctx->graph) { cudaGraphExecDestroy(ctx->graph); ctx->graph = nullptr; }
+	// (the cached graph: see set_uniform_mass, which every upload path goes through)
 	if (ctx->P2)  // pad rows and masses of the second stage buffer
 		CK(cudaMemcpy(ctx->P2, ctx->P, (size_t)ctx->n_pad * 4 * ctx->esz, cudaMemcpyDeviceToDevice));
 	if (ctx->p2p) {	 // peers read this rank's block of Y from here on: publish it
@@ -1326,8 +1337,7 @@ int nbody_upload_aos_owned(nbody_ctx* ctx, const void* owned_bodies) {
 	CK(cudaMemcpyAsync(mm, ctx->d_norms, sizeof mm, cudaMemcpyDeviceToHost, ctx->sc));
 	CK(cudaStreamSynchronize(ctx->sc));
 	const bool uni = ctx->opt_unimass != 0 && mm[0] == -mm[1] && std::isfinite(mm[0]);
-	ctx->unimass = uni;
-	ctx->uniform_mass = uni ? mm[0] : 0.;
+	set_uniform_mass(ctx, uni, mm[0]);
 	const unsigned g = (ctx->own_pad + 255) / 256;
 	if (ctx->prec == 64)
 		NB_LAUNCH(pack_aos_owned_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
@@ -1453,6 +1463,7 @@ static int step_impl(nbody_ctx* ctx, const StepCoef& k, int graph_key, double ta
 			CK(ce);
 			CK(cudaGraphInstantiate(&ctx->graph, g, 0));
 			cudaGraphDestroy(g);
+			++ctx->graph_captures;
 			ctx->graph_scheme = graph_key;
 			ctx->graph_tau = tau;
 		}
@@ -1639,6 +1650,7 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 	}
 	ctx->tm.uniform_mass = ctx->unimass ? 1u : 0u;
 	ctx->tm.pair_symmetry = sym_in_use(ctx) ? 1u : 0u;
+	ctx->tm.graph_captures = ctx->graph_captures;
 	ctx->tm.sym_variant = 0;
 	if (sym_in_use(ctx)) {
 		const SymVariant* tab = ctx->prec == 64 ? g_sym64 : g_sym32;

@@ -462,18 +462,24 @@ def test_emulated_cxx_driver_reference_run_and_schemes(emulated_driver, golden, 
 
 def test_emulated_graph_is_not_replayed_across_uploads(oracle):
     """A captured step holds the uniform mass by value: re-uploading the same bodies with a
-    DIFFERENT equal mass on one context must not replay the old graph."""
+    DIFFERENT equal mass on one context must not replay the old graph; an
+    upload that changes nothing the capture holds keeps it."""
     n = 64
     b = generators.uniform_bodies(n, seed=2)
+    general = b[:, 0].copy()
     with capi.Context(n, 64) as ctx:
         ctx.set_option("use_graph", 1)
-        for mass in (1e9, 3e9):
-            b[:, 0] = mass
+        # (masses, graph captures expected so far): the same state uploaded again keeps the graph,
+        # another equal mass, distinct masses, and equal masses again each drop it
+        for mass, captures in ((1e9, 1), (1e9, 1), (3e9, 2), (None, 3), (None, 3), (1e9, 4)):
+            b[:, 0] = general if mass is None else mass
             want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, max_steps=3, rows=False)
             ctx.upload_aos(b)
             ctx.step(capi.NBODY_RK4, 0.1, 3, sync=True)
             got = ctx.download_aos()
-            assert ctx.timing().uniform_mass == 1
+            tm = ctx.timing()
+            assert tm.uniform_mass == (0 if mass is None else 1)
+            assert tm.graph_captures == captures
             check_state(got, want, b, 1e-10)
 
 

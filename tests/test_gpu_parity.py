@@ -442,14 +442,22 @@ def test_python_host_mirror_writes_reference_files(golden, tmp_path):
 
 def test_graph_is_not_replayed_across_uploads(oracle):
     """Re-upload with a different equal mass on one context, stepping through the CUDA-graph path:
-    the captured step bakes the uniform mass into K2's parameters, so the graph must be dropped."""
+    the captured step bakes the uniform mass into K2's parameters, so the graph must be dropped;
+    an upload that changes nothing the capture holds keeps it (the end-to-end loop's case)."""
     n = 64
     b = generators.uniform_bodies(n, seed=2)
+    general = b[:, 0].copy()
     with capi.Context(n, 64) as ctx:
         ctx.set_option("use_graph", 1)
-        for mass in (1e9, 3e9):
-            b[:, 0] = mass
+        # (masses, graph captures expected so far): the same state uploaded again keeps the graph,
+        # another equal mass, distinct masses, and equal masses again each drop it
+        for mass, captures in ((1e9, 1), (1e9, 1), (3e9, 2), (None, 3), (None, 3), (1e9, 4)):
+            b[:, 0] = general if mass is None else mass
             want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, max_steps=3, rows=False)
             ctx.upload_aos(b)
             ctx.step(capi.NBODY_RK4, 0.1, 3, sync=True)
-            check_state(ctx.download_aos().astype(np.float64), want, b, TOL64_TRAJ, steps=3)
+            got = ctx.download_aos()
+            tm = ctx.timing()
+            assert tm.uniform_mass == (0 if mass is None else 1)
+            assert tm.graph_captures == captures
+            check_state(got.astype(np.float64), want, b, TOL64_TRAJ, steps=3)
