@@ -59,6 +59,10 @@ typedef struct nbody_timing {
 									(option "use_graph") is captured once per scheme, tau and mass
 									state, and again only after an option, parameter or upload
 									changed what the capture holds by value */
+	uint32_t deterministic;		 /* 1 if the row sums of the force kernel in use do not depend on
+									scheduling: the one-sided kernel (fixed order) or the
+									pair-symmetric kernel with option "deterministic" */
+	uint32_t reserved0;
 } nbody_timing;
 
 /* Option "trace" = 1: every operation a call enqueues (force launch, fused stage kernel, memsets,
@@ -132,7 +136,15 @@ int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab
  * reduce-scattered (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose
  * block divides the per-rank block of nbody_partition, a forced variant that does not is
  * NBODY_ERR_STATE).  nbody_timing.pair_symmetry reports which kernel ran),
- * "sym_variant" (kernel variant id of that mode, -1 = default). */
+ * "sym_variant" (kernel variant id of that mode, -1 = default),
+ * "deterministic" (0 default / 1; set before the upload): the pair-symmetric kernel adds every
+ * unit's share of a row as an exact FIXED-POINT integer (192-bit window derived from n, the
+ * largest mass and eps; 64-bit integer atomics) instead of a floating-point atomic, and the stage
+ * kernel rounds each row sum to T once: BIT-REPRODUCIBLE run to run whatever the scheduling, on
+ * any number of GPUs (the reduce-scatter sums integers), same tolerances against the reference.
+ * NBODY_ERR_STATE from the step / RHS call if eps == 0 or the input's dynamic range does not fit
+ * the window.  No effect where the one-sided kernel runs (it is bit-reproducible as it is).
+ * nbody_timing.deterministic reports what the kernel in use guarantees). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 
 /* Rows [begin,end) this rank owns (lab_4's offsets[id], counts[id],

@@ -33,7 +33,8 @@ class Timing(C.Structure):
                 ("interactions", C.c_uint64), ("steps_done", C.c_uint64),
                 ("uniform_mass", C.c_uint32), ("variant", C.c_uint32),
                 ("pair_evaluations", C.c_uint64), ("pair_symmetry", C.c_uint32),
-                ("sym_variant", C.c_uint32), ("graph_captures", C.c_uint64)]
+                ("sym_variant", C.c_uint32), ("graph_captures", C.c_uint64),
+                ("deterministic", C.c_uint32), ("reserved0", C.c_uint32)]
 
 
 class TraceEntry(C.Structure):

@@ -28,6 +28,7 @@
 //    in strip-local accumulators (zeroed per strip) and are committed to the running i-side sums
 //    in shared memory afterwards, so a redo needs no backup registers.
 #pragma once
+#include "fixed_sums.cuh"
 #include "force_kernels.cuh"
 #include "sym_schedule.h"
 
@@ -81,6 +82,8 @@ struct SymParams {
 	unsigned* counter;	 // work-unit ticket counter, zeroed before the launch
 	double pad_pos;		 // coordinates given to i-rows >= n_pad (see pack_aos_kernel)
 	unsigned pos_rows;	 // rows allocated in pos (bounds asserts only)
+	int fx_e0;			 // ACC = 2 only: exponent of the lowest bit of the fixed-point row sums; `aj` is
+						 //   then uint64[FX_PLANES][rows_pad] (fixed_sums.cuh) instead of T[3][rows_pad]
 };
 
 // One j-body (travelling with its accumulator) against the I i-bodies of this thread.
@@ -98,6 +101,9 @@ __device__ __forceinline__ float sym_add(float a, float b) { return __fadd_rn(a,
 // evaluation ran at 2.26 cycles each (1565 vs 1718 G int/s, profiles/r02_experiment_acc_muladd.jsonl),
 // the 18-instruction build at 2.40: the pipe delivers ~84-88 % for this instruction stream either
 // way.  The template parameter stays for the record; no variant table entry uses it.
+// ACC = 2 (option "deterministic"): the pair arithmetic of ACC = 0; what changes is how a unit's
+// sums reach the global row sums -- as exact fixed-point integers (fixed_sums.cuh) instead of
+// floating-point RED, so the result does not depend on the order in which units finish.
 template <typename T, int I, int ORD, bool UM, bool EXACT, int ACC = 0>
 __device__ __forceinline__ void interact_sym(const T jx, const T jy, const T jz, const T jm,
 											  const T (&xi)[I], const T (&yi)[I], const T (&zi)[I],
@@ -172,6 +178,18 @@ __device__ __forceinline__ void sym_strip(const typename V4<T>::type* strip, con
 		ajy = __shfl_sync(0xffffffffu, ajy, next_lane);
 		ajz = __shfl_sync(0xffffffffu, ajz, next_lane);
 	}
+}
+
+// ACC = 2: one row's share of a unit (or of a warp's strip) goes to the fixed-point row sums.
+template <typename T>
+__device__ __forceinline__ void sym_commit_fx(const SymParams& p, const unsigned row, const T ax,
+											   const T ay, const T az) {
+	unsigned long long* planes = reinterpret_cast<unsigned long long*>(p.aj);
+	const size_t stride = p.rows_pad;
+	unsigned long long* poison = planes + (size_t)(3 * FX_LIMBS) * stride + row;
+	fx_add(planes + row, stride, poison, (double)ax, p.fx_e0);
+	fx_add(planes + (size_t)FX_LIMBS * stride + row, stride, poison, (double)ay, p.fx_e0);
+	fx_add(planes + (size_t)(2 * FX_LIMBS) * stride + row, stride, poison, (double)az, p.fx_e0);
 }
 
 template <typename T, int THREADS, int I, int STAGES>
@@ -298,9 +316,13 @@ __global__ void __launch_bounds__(THREADS, MINB)
 																		   next_lane);
 					const unsigned j = j_first + (unsigned)s0 + (unsigned)(tid & 31);
 					NB_CHECK(j < p.rows_pad);
-					atomicAdd(gjx + j, ajx);  // result unused -> RED.ADD
-					atomicAdd(gjy + j, ajy);
-					atomicAdd(gjz + j, ajz);
+					if (ACC == 2) {
+						sym_commit_fx<T>(p, j, ajx, ajy, ajz);
+					} else {
+						atomicAdd(gjx + j, ajx);  // result unused -> RED.ADD
+						atomicAdd(gjy + j, ajy);
+						atomicAdd(gjz + j, ajz);
+					}
 #pragma unroll
 					for (int k = 0; k < I; ++k) {
 						accm[(0 * I + k) * THREADS + tid] += loc.x[k];
@@ -328,9 +350,14 @@ __global__ void __launch_bounds__(THREADS, MINB)
 		for (int k = 0; k < I; ++k) {
 			const unsigned row = row0 + k * THREADS;	 // < rows_pad = nb * BLOCK
 			NB_CHECK(row < p.rows_pad);
-			atomicAdd(gjx + row, accm[(0 * I + k) * THREADS + tid]);  // result unused -> RED.ADD
-			atomicAdd(gjy + row, accm[(1 * I + k) * THREADS + tid]);
-			atomicAdd(gjz + row, accm[(2 * I + k) * THREADS + tid]);
+			if (ACC == 2) {
+				sym_commit_fx<T>(p, row, accm[(0 * I + k) * THREADS + tid],
+								 accm[(1 * I + k) * THREADS + tid], accm[(2 * I + k) * THREADS + tid]);
+			} else {
+				atomicAdd(gjx + row, accm[(0 * I + k) * THREADS + tid]);  // result unused -> RED.ADD
+				atomicAdd(gjy + row, accm[(1 * I + k) * THREADS + tid]);
+				atomicAdd(gjz + row, accm[(2 * I + k) * THREADS + tid]);
+			}
 		}
 		if (tid == 0) *next_unit_s = next_ticket;
 		__syncthreads();

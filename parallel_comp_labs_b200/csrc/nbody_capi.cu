@@ -36,7 +36,8 @@ namespace {
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-enum { NCCL_INT8 = 0, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2, NCCL_MIN = 3 };
+enum { NCCL_INT8 = 0, NCCL_UINT64 = 5, NCCL_FLOAT = 7, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2,
+	   NCCL_MIN = 3 };
 struct NcclApi {
 	void* lib = nullptr;
 	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
@@ -134,6 +135,7 @@ struct SymVariant {
 	const void* fn[2];	// [0] general masses, [1] uniform mass factored out
 	void (*launch[2])(dim3, cudaStream_t, size_t, const SymParams&, double eps2);
 	const char* name;
+	bool fx;  // ACC = 2: fixed-point row sums (option "deterministic", fixed_sums.cuh)
 };
 template <typename T, int TH, int I, int ST, int MB, int UM, int ORD, int ROT, int ACC>
 void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p, double eps2) {
@@ -146,8 +148,9 @@ void launch_force_sym(dim3 grid, cudaStream_t s, size_t smem, const SymParams& p
 				  (const void*)force_sym_kernel<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},           \
 				 {launch_force_sym<T, TH, I, ST, MB, 0, ORD, ROT, ACC>,                         \
 				  launch_force_sym<T, TH, I, ST, MB, 1, ORD, ROT, ACC>},                        \
-				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT "/acc" #ACC }
+				 #T "/sym/t" #TH "/i" #I "/s" #ST "/b" #MB "/o" #ORD "/rot" #ROT "/acc" #ACC, ACC == 2 }
 #define NB_SYM_VARIANT(T, TH, I, ST, MB, ORD, ROT) NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, 0)
+#define NB_SYM_VARIANT_FX(T, TH, I, ST, MB, ORD, ROT) NB_SYM_VARIANT_A(T, TH, I, ST, MB, ORD, ROT, 2)
 // {threads, i-bodies per thread, ring stages, min CTAs/SM, correction order, rot}
 // rot = 0: the j-body is shuffled round the warp with its accumulator; rot = 1: it is re-read
 // from the staged tile and only the accumulator is shuffled (force_sym_kernels.cuh, sym_strip).
@@ -166,7 +169,17 @@ const SymVariant g_sym64[] = {
 	// halves the partition and tail granularity (profiles/r02_sym_sweep2.md)
 	NB_SYM_VARIANT(double, 64, 8, 2, 6, 2, 1),	 // 9: 512-row blocks
 	NB_SYM_VARIANT(double, 64, 4, 2, 10, 2, 1),	 // 10: 256-row blocks
+	// 11-15: the builds the automatic choice uses (8, 9, 7, 5, 3) with fixed-point row sums
+	// (option "deterministic": the same pair arithmetic, order-independent sums across units)
+	NB_SYM_VARIANT_FX(double, 128, 8, 2, 3, 2, 1),
+	NB_SYM_VARIANT_FX(double, 64, 8, 2, 6, 2, 1),
+	NB_SYM_VARIANT_FX(double, 128, 6, 2, 4, 2, 1),
+	NB_SYM_VARIANT_FX(double, 128, 4, 2, 5, 2, 1),
+	NB_SYM_VARIANT_FX(double, 128, 2, 2, 8, 2, 0),
 };
+// deterministic twin of each entry: the fixed-point build with the same block size (an fx entry
+// is its own twin)
+const int g_sym64_fx_twin[] = {14, 14, 13, 15, 11, 14, 14, 13, 11, 12, 15, 11, 12, 13, 14, 15};
 const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 0),
 	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 0),
@@ -174,9 +187,17 @@ const SymVariant g_sym32[] = {
 	NB_SYM_VARIANT(float, 128, 4, 2, 8, 2, 1),
 	NB_SYM_VARIANT(float, 128, 8, 2, 5, 2, 1),
 	NB_SYM_VARIANT(float, 64, 8, 2, 10, 2, 1),	// 5: 64-thread CTAs, 512-row blocks
+	// 6-9: entries 1, 5, 3, 2 with fixed-point row sums (option "deterministic")
+	NB_SYM_VARIANT_FX(float, 128, 8, 2, 5, 2, 0),
+	NB_SYM_VARIANT_FX(float, 64, 8, 2, 10, 2, 1),
+	NB_SYM_VARIANT_FX(float, 128, 4, 2, 8, 2, 1),
+	NB_SYM_VARIANT_FX(float, 128, 2, 2, 8, 2, 0),
 };
+const int g_sym32_fx_twin[] = {8, 6, 9, 8, 6, 7, 6, 7, 8, 9};
 constexpr int N_SYM64 = sizeof(g_sym64) / sizeof(SymVariant);
 constexpr int N_SYM32 = sizeof(g_sym32) / sizeof(SymVariant);
+static_assert(sizeof(g_sym64_fx_twin) / sizeof(int) == N_SYM64, "one twin entry per FP64 build");
+static_assert(sizeof(g_sym32_fx_twin) / sizeof(int) == N_SYM32, "one twin entry per FP32 build");
 constexpr unsigned SYM_EXTRA_TILES = 4;	 // rows allocated past n_pad: phantom tiles of the last block
 constexpr int N_VAR64 = sizeof(g_var64) / sizeof(Variant);
 constexpr int N_VAR32 = sizeof(g_var32) / sizeof(Variant);
@@ -196,9 +217,16 @@ struct nbody_ctx {
 		 *d_aos = nullptr;
 	unsigned apart_slices = 0;
 	size_t apart_bytes = 0;
-	void* aj = nullptr;		 // T[3][aj_rows] j-side sums of the pair-symmetric kernel
-	unsigned aj_rows = 0;
+	void* aj = nullptr;		 // T[3][rows] row sums of the pair-symmetric kernel (fixed-point builds:
+	size_t aj_bytes = 0;	 // uint64[FX_PLANES][rows])
 	long opt_pair_symmetry = -1, opt_sym_variant = -1;
+	// option "deterministic": fixed-point row sums.  What the window needs to know about the input,
+	// scanned at upload: largest |mass|, smallest non-zero |mass|, largest |coordinate|.
+	long opt_deterministic = 0;
+	bool stats_valid = false;
+	double m_absmax = 0., m_absmin = 0., coord_absmax = 0.;
+	int fx_e0 = 0;			 // window in use by the cached graph / the last plan
+	bool fx_e0_valid = false;
 	// general tableaux (nbody_step_rk / nbody_step_embedded): resident stage derivatives, the
 	// norms of the last embedded step, and the state before it (nbody_step_undo)
 	void *kr = nullptr, *kv = nullptr;
@@ -317,11 +345,14 @@ const Variant& variant_of(const nbody_ctx* c) {
 //   FP64 general masses N >= 512k: 7 1529 | 9 1525 | 5 1518 | 8 1472;  N = 64k-256k: 9 >= 5 >= 7;  below: 5
 //   FP32 equal masses   N >= 16k: 1 (I=8, shuffled j);  general masses: 5 (64 threads, I=8, re-read j);  N <= 12k: 3
 // On several GPUs the size that matters is the per-rank share of the pairs: n / sqrt(world).
+// Option "deterministic" = 1 then swaps the choice for its fixed-point twin (same block size).
 const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
 	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
+	const int* twin = c->prec == 64 ? g_sym64_fx_twin : g_sym32_fx_twin;
+	const bool det = c->opt_deterministic != 0;
 	long v = c->opt_sym_variant;
-	if (v >= 0 && v < nv) return tab[v];
+	if (v >= 0 && v < nv) return tab[det ? twin[v] : v];
 	const double n_eff = (double)c->n / std::sqrt((double)c->world);
 	// per-size winners of profiles/r02_sym_crossover.md and r02_sym_sweep3.md
 	static const int p64_small[] = {3, 3, 3}, p64_mid[] = {5, 3, 3}, p64_fine[] = {9, 5, 3},
@@ -333,10 +364,53 @@ const SymVariant& sym_variant_of(const nbody_ctx* c) {
 	else if (c->unimass) pref = n_eff < 26000 ? p64_mid : n_eff < 400000 ? p64_fine : p64_um;
 	else pref = n_eff < 50000 ? p64_mid : (n_eff < 500000 || c->world > 1) ? p64_fine : p64_gen;
 	for (int k = 0; k < 3; ++k) {
-		const SymVariant& sv = tab[pref[k]];
+		const SymVariant& sv = tab[det ? twin[pref[k]] : pref[k]];
 		if (c->world == 1 || c->own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
 	}
-	return tab[pref[2]];
+	return tab[det ? twin[pref[2]] : pref[2]];
+}
+
+// Window of the fixed-point row sums (fixed_sums.cuh): the top comes from a rigorous bound on any
+// single contribution -- a unit's share of a row is at most n pair terms, each at most
+// m_max |d| / max(|d|, eps)^3 <= m_max / eps^2 (m = 1 with the mass factored out) -- and the lowest
+// bit lies FX_WINDOW_BITS below it.  Refused (the caller reports it) when the window would not
+// leave 60 bits under the SMALLEST pair term the input can produce, m_min / D^2 with D the
+// diagonal of the bounding box at upload: the sums would silently lose precision.
+int fx_window(const nbody_ctx* c, int* e0, std::string* why) {
+	if (!c->stats_valid) {
+		*why = "option \"deterministic\" must be set before the upload (the window of the "
+			   "fixed-point sums is derived from the uploaded masses and positions)";
+		return NBODY_ERR_STATE;
+	}
+	const double eps2 = c->eps * c->eps;
+	const double mmax = c->unimass ? 1. : c->m_absmax, mmin = c->unimass ? 1. : c->m_absmin;
+	if (!(eps2 > 0.) || !std::isfinite(1. / eps2) || !std::isfinite(mmax)) {
+		*why = "option \"deterministic\" needs eps > 0 (eps^2 representable) and finite masses: the "
+			   "fixed-point window is bounded by n m_max / eps^2";
+		return NBODY_ERR_STATE;
+	}
+	int ex = 0;
+	// log2 of the bound, rounded up, + 2 bits for the rounding of the pair arithmetic
+	std::frexp(mmax > 0. ? mmax : 1., &ex);
+	int top = ex;
+	std::frexp(1. / eps2, &ex);
+	top += ex;
+	std::frexp((double)c->n, &ex);
+	top += ex + 2;
+	*e0 = top - FX_WINDOW_BITS;
+	if (c->coord_absmax > 0. && mmin > 0.) {
+		int em = 0, ed = 0;
+		std::frexp(mmin, &em);					 // mmin >= 2^(em-1)
+		std::frexp(4. * c->coord_absmax, &ed);	 // D <= 2 sqrt(3) max|coordinate| < 2^ed
+		const int smallest = (em - 1) - 2 * ed;	 // log2 of a lower bound of m_min / D^2
+		if (*e0 + 60 > smallest) {
+			*why = "option \"deterministic\": the dynamic range of this input (n m_max / eps^2 against "
+				   "m_min / D^2) does not fit the " + std::to_string(FX_WINDOW_BITS) +
+				   "-bit fixed-point window; use pair_symmetry = 0 for bit-reproducible sums";
+			return NBODY_ERR_STATE;
+		}
+	}
+	return NBODY_OK;
 }
 
 // Which force kernel runs.  Option "pair_symmetry": 1 = the pair-symmetric kernel, 0 = the
@@ -397,7 +471,15 @@ struct LaunchPlan {
 	bool sym;
 	unsigned nb, tpb, rows_pad;	 // blocks of the whole problem, tiles per block, nb * block rows
 	unsigned block0, nb_own;	 // blocks this rank owns
+	bool fx;					 // fixed-point row sums (SymVariant::fx), window exponent fx_e0
+	int fx_e0;
 };
+
+// bytes of the row-sum array of the pair-symmetric kernel
+size_t sym_sum_bytes(const nbody_ctx* ctx, const LaunchPlan& lp) {
+	return lp.fx ? (size_t)FX_PLANES * lp.rows_pad * sizeof(unsigned long long)
+				 : (size_t)3 * lp.rows_pad * ctx->esz;
+}
 
 int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
 	// the pair-symmetric kernel adds both sides of every pair into `aj`: no partial-sum rows
@@ -411,13 +493,14 @@ int ensure_apart(nbody_ctx* ctx, const LaunchPlan& lp) {
 		ctx->apart_bytes = bytes;
 	}
 	ctx->apart_slices = lp.sym ? 0 : lp.s_local + lp.s_remote;
-	if (lp.sym && lp.rows_pad > ctx->aj_rows) {
+	const size_t aj_bytes = lp.sym ? sym_sum_bytes(ctx, lp) : 0;
+	if (aj_bytes > ctx->aj_bytes) {
 		CK(cudaStreamSynchronize(ctx->sc));
 		if (ctx->aj) CK(cudaFree(ctx->aj));
 		ctx->aj = nullptr;
-		ctx->aj_rows = 0;
-		CK(cudaMalloc(&ctx->aj, (size_t)3 * lp.rows_pad * ctx->esz));
-		ctx->aj_rows = lp.rows_pad;
+		ctx->aj_bytes = 0;
+		CK(cudaMalloc(&ctx->aj, aj_bytes));
+		ctx->aj_bytes = aj_bytes;
 	}
 	return NBODY_OK;
 }
@@ -452,9 +535,24 @@ uint64_t sym_pair_evaluations(unsigned n_real, unsigned nb, unsigned tpb, unsign
 
 int make_plan(nbody_ctx* ctx, LaunchPlan* lp) {
 	lp->sym = sym_in_use(ctx);
+	lp->fx = false;
+	lp->fx_e0 = 0;
 	if (lp->sym) {
 		const SymVariant& sv = sym_variant_of(ctx);
 		const unsigned TJ = 256, block = sv.threads * sv.ipt;
+		if (sv.fx) {
+			std::string why;
+			const int rc = fx_window(ctx, &lp->fx_e0, &why);
+			if (rc) return fail(ctx, rc, why);
+			lp->fx = true;
+			// a captured step holds the window by value
+			if (ctx->graph && (!ctx->fx_e0_valid || ctx->fx_e0 != lp->fx_e0)) {
+				cudaGraphExecDestroy(ctx->graph);
+				ctx->graph = nullptr;
+			}
+			ctx->fx_e0 = lp->fx_e0;
+			ctx->fx_e0_valid = true;
+		}
 		if (ctx->world > 1 && ctx->p2p)
 			return fail(ctx, NBODY_ERR_STATE,
 						"option \"pair_symmetry\" is not available with the peer-pull exchange");
@@ -591,7 +689,7 @@ int launch_force_range(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf, bool 
 int sym_prepare(nbody_ctx* ctx, const LaunchPlan& lp) {
 	const int tr = trace_begin(ctx, ctx->sc, NBODY_TRACE_MEMSET);
 	CK(cudaMemsetAsync(ctx->d_counters, 0, sizeof(unsigned), ctx->sc));
-	CK(cudaMemsetAsync(ctx->aj, 0, (size_t)3 * lp.rows_pad * ctx->esz, ctx->sc));
+	CK(cudaMemsetAsync(ctx->aj, 0, sym_sum_bytes(ctx, lp), ctx->sc));
 	trace_end(ctx, ctx->sc, tr);
 	return NBODY_OK;
 }
@@ -613,6 +711,7 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	p.counter = ctx->d_counters;
 	p.pad_pos = ctx->unimass ? (ctx->prec == 64 ? 1e150 : 1e18) : 0.;
 	p.pos_rows = ctx->n_pad + SYM_EXTRA_TILES * PAD_UNIT;
+	p.fx_e0 = lp.fx_e0;
 	// (the ticket counter and the row sums were zeroed by sym_prepare, before the wait for the
 	// exchange, so that the memsets overlap the all-gather)
 	const unsigned long long units = (unsigned long long)lp.nb_own * lp.s_local;
@@ -640,12 +739,16 @@ int launch_force_sym_all(nbody_ctx* ctx, const LaunchPlan& lp, StageBuf buf) {
 	if (ctx->world > 1) {
 		// every rank has collected reactions for ALL bodies its walk touched: sum them over the
 		// ranks, each rank keeping the rows it owns (in place: rows_pad == world * own_pad here)
-		const int dt = ctx->prec == 64 ? NCCL_DOUBLE : NCCL_FLOAT;
+		// (fixed-point sums: integer limbs, so the order in which NCCL adds the ranks' shares does not
+		// matter either)
+		const int dt = lp.fx ? NCCL_UINT64 : ctx->prec == 64 ? NCCL_DOUBLE : NCCL_FLOAT;
+		const size_t esz = lp.fx ? sizeof(unsigned long long) : ctx->esz;
+		const int planes = lp.fx ? FX_PLANES : 3;
 		const int tr2 = trace_begin(ctx, ctx->sc, NBODY_TRACE_REDUCE);
 		CKN(g_nccl.GroupStart());
-		for (int c = 0; c < 3; ++c) {
-			char* base = (char*)ctx->aj + (size_t)c * lp.rows_pad * ctx->esz;
-			CKN(g_nccl.ReduceScatter(base, base + (size_t)ctx->rank * ctx->own_pad * ctx->esz,
+		for (int c = 0; c < planes; ++c) {
+			char* base = (char*)ctx->aj + (size_t)c * lp.rows_pad * esz;
+			CKN(g_nccl.ReduceScatter(base, base + (size_t)ctx->rank * ctx->own_pad * esz,
 									 ctx->own_pad, dt, NCCL_SUM, ctx->comm, ctx->sc));
 		}
 		CKN(g_nccl.GroupEnd());
@@ -762,6 +865,8 @@ int launch_stage(nbody_ctx* ctx, const LaunchPlan& lp, void* rhs_out, void* next
 	p.apart_stride = lp.apart_stride;
 	p.aj = lp.sym ? ctx->aj : nullptr;
 	p.aj_stride = lp.rows_pad;
+	p.aj_fx = lp.fx ? 1 : 0;
+	p.aj_e0 = lp.fx_e0;
 	p.mass_scale = ctx->unimass ? (T)ctx->uniform_mass : T(1);
 	p.minusG = (T)(-(T)ctx->G);
 	p.c_next = (T)c_next;
@@ -809,6 +914,8 @@ int launch_stage_general(nbody_ctx* ctx, const LaunchPlan& lp, void* next_buf, c
 	p.apart_stride = lp.apart_stride;
 	p.aj = lp.sym ? ctx->aj : nullptr;
 	p.aj_stride = lp.rows_pad;
+	p.aj_fx = lp.fx ? 1 : 0;
+	p.aj_e0 = lp.fx_e0;
 	p.mass_scale = ctx->unimass ? (T)ctx->uniform_mass : T(1);
 	p.minusG = (T)(-(T)ctx->G);
 	p.c_next = p.b = p.final_scale = T(0);
@@ -1219,6 +1326,13 @@ int nbody_set_option(nbody_ctx* ctx, const char* name, long value) {
 		if (value < -1 || value >= nv) return fail(ctx, NBODY_ERR_ARG, "sym_variant out of range");
 		ctx->opt_sym_variant = value;
 	}
+	else if (k == "deterministic") {
+		// fixed-point row sums in the pair-symmetric kernel (the one-sided kernel is bit-reproducible
+		// as it is); the window needs the input statistics gathered by the NEXT upload
+		if (ctx->uploaded && value != 0 && !ctx->stats_valid)
+			return fail(ctx, NBODY_ERR_STATE, "set \"deterministic\" before the upload");
+		ctx->opt_deterministic = value != 0;
+	}
 	else if (k == "unimass") {
 		if (ctx->uploaded) return fail(ctx, NBODY_ERR_STATE, "set \"unimass\" before the upload");
 		ctx->opt_unimass = value;
@@ -1248,6 +1362,42 @@ static void set_uniform_mass(nbody_ctx* ctx, bool uni, double m0) {
 	}
 	ctx->unimass = uni;
 	ctx->uniform_mass = um;
+}
+
+// Option "deterministic": what fx_window needs to know about the input -- largest |mass|, smallest
+// non-zero |mass|, largest |coordinate| -- over `count` bodies whose masses are `mstride` elements
+// apart and whose x,y,z start at `coords` and are `cstride` elements apart.  acc = {max|m|,
+// min|m| != 0 (HUGE_VAL if none), max|x|}; non-finite values are left to the kernels (poison word).
+static void scan_stats(nbody_ctx* ctx, const void* masses, size_t mstride, const void* coords,
+					   size_t cstride, size_t count, double acc[3]) {
+	const bool f64 = ctx->prec == 64;
+	auto at = [f64](const void* base, size_t idx) {
+		return f64 ? ((const double*)base)[idx] : (double)((const float*)base)[idx];
+	};
+	double mx = acc[0], mn = acc[1], cx = acc[2];
+	for (size_t i = 0; i < count; ++i) {
+		const double m = std::fabs(at(masses, i * mstride));
+		if (m > mx) mx = m;
+		if (m > 0. && m < mn) mn = m;
+		const double a = std::max(std::fabs(at(coords, i * cstride)),
+								  std::max(std::fabs(at(coords, i * cstride + 1)),
+										   std::fabs(at(coords, i * cstride + 2))));
+		if (std::isfinite(a) && a > cx) cx = a;
+	}
+	acc[0] = mx; acc[1] = mn; acc[2] = cx;
+}
+// the fixed-point builds are asked for: option "deterministic", or an fx entry named explicitly
+static bool wants_fx(const nbody_ctx* ctx) {
+	if (ctx->opt_deterministic) return true;
+	const int nv = ctx->prec == 64 ? N_SYM64 : N_SYM32;
+	const long v = ctx->opt_sym_variant;
+	return v >= 0 && v < nv && (ctx->prec == 64 ? g_sym64 : g_sym32)[v].fx;
+}
+static void set_stats(nbody_ctx* ctx, const double acc[3]) {
+	ctx->m_absmax = acc[0];
+	ctx->m_absmin = acc[1] == HUGE_VAL ? 0. : acc[1];
+	ctx->coord_absmax = acc[2];
+	ctx->stats_valid = true;
 }
 
 // Every body has the same mass (e.g. the Plummer configs, the 4-body test)?  Then the mass is
@@ -1293,6 +1443,12 @@ int nbody_upload_aos(nbody_ctx* ctx, const void* bodies) {
 	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, bytes + 64));
 	CK(cudaMemcpyAsync(ctx->d_aos, bodies, bytes, cudaMemcpyHostToDevice, ctx->sc));
 	detect_uniform_mass(ctx, bodies, 7);
+	ctx->stats_valid = false;
+	if (wants_fx(ctx)) {
+		double acc[3] = {0., HUGE_VAL, 0.};
+		scan_stats(ctx, bodies, 7, (const char*)bodies + ctx->esz, 7, ctx->n, acc);
+		set_stats(ctx, acc);
+	}
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
 		NB_LAUNCH(pack_aos_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
@@ -1323,7 +1479,15 @@ int nbody_upload_aos_owned(nbody_ctx* ctx, const void* owned_bodies) {
 	if (!ctx->d_aos) CK(cudaMalloc(&ctx->d_aos, ctx->n * 7 * ctx->esz + 64));
 	if (bytes) CK(cudaMemcpyAsync(ctx->d_aos, owned_bodies, bytes, cudaMemcpyHostToDevice, ctx->sc));
 	// equal masses everywhere?  min / max of the masses, all-reduced (MIN over {min, -max})
-	double mm[2] = {HUGE_VAL, HUGE_VAL};
+	// (+ with option "deterministic" the input statistics of fx_window: {-max|m|, min|m| != 0,
+	// -max|coordinate|} ride along)
+	double mm[5] = {HUGE_VAL, HUGE_VAL, 0., HUGE_VAL, 0.};
+	ctx->stats_valid = false;
+	if (wants_fx(ctx) && ctx->own_real) {
+		double acc[3] = {0., HUGE_VAL, 0.};
+		scan_stats(ctx, owned_bodies, 7, (const char*)owned_bodies + ctx->esz, 7, ctx->own_real, acc);
+		mm[2] = -acc[0]; mm[3] = acc[1]; mm[4] = -acc[2];
+	}
 	for (unsigned i = 0; i < ctx->own_real; ++i) {
 		const double m = ctx->prec == 64 ? ((const double*)owned_bodies)[7 * (size_t)i]
 										  : (double)((const float*)owned_bodies)[7 * (size_t)i];
@@ -1331,11 +1495,15 @@ int nbody_upload_aos_owned(nbody_ctx* ctx, const void* owned_bodies) {
 		mm[0] = std::min(mm[0], m);
 		mm[1] = std::min(mm[1], -m);
 	}
-	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 4 * sizeof(double)));
+	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 8 * sizeof(double)));
 	CK(cudaMemcpyAsync(ctx->d_norms, mm, sizeof mm, cudaMemcpyHostToDevice, ctx->sc));
-	CKN(g_nccl.AllReduce(ctx->d_norms, ctx->d_norms, 2, NCCL_DOUBLE, NCCL_MIN, ctx->comm, ctx->sc));
+	CKN(g_nccl.AllReduce(ctx->d_norms, ctx->d_norms, 5, NCCL_DOUBLE, NCCL_MIN, ctx->comm, ctx->sc));
 	CK(cudaMemcpyAsync(mm, ctx->d_norms, sizeof mm, cudaMemcpyDeviceToHost, ctx->sc));
 	CK(cudaStreamSynchronize(ctx->sc));
+	if (wants_fx(ctx)) {
+		const double acc[3] = {-mm[2], mm[3], -mm[4]};
+		set_stats(ctx, acc);
+	}
 	const bool uni = ctx->opt_unimass != 0 && mm[0] == -mm[1] && std::isfinite(mm[0]);
 	set_uniform_mass(ctx, uni, mm[0]);
 	const unsigned g = (ctx->own_pad + 255) / 256;
@@ -1379,6 +1547,12 @@ int nbody_upload_soa(nbody_ctx* ctx, const void* m, const void* r4, const void* 
 	CK(cudaMemcpyAsync(dr, r4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
 	CK(cudaMemcpyAsync(dv, v4, n * 4 * e, cudaMemcpyHostToDevice, ctx->sc));
 	detect_uniform_mass(ctx, m, 1);
+	ctx->stats_valid = false;
+	if (wants_fx(ctx)) {
+		double acc[3] = {0., HUGE_VAL, 0.};
+		scan_stats(ctx, m, 1, r4, 4, ctx->n, acc);
+		set_stats(ctx, acc);
+	}
 	const unsigned g = (ctx->n_pad + 255) / 256;
 	if (ctx->prec == 64)
 		NB_LAUNCH(pack_soa_kernel<double>, dim3(g), dim3(256), 0, ctx->sc,
@@ -1585,7 +1759,7 @@ int nbody_step_embedded(nbody_ctx* ctx, int n_stages, const double* a, const dou
 		CK(cudaMalloc(&ctx->undo_Y, (size_t)ctx->n_pad * v4));
 		CK(cudaMalloc(&ctx->undo_vel, (size_t)ctx->own_pad * v4));
 	}
-	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 4 * sizeof(double)));
+	if (!ctx->d_norms) CK(cudaMalloc(&ctx->d_norms, 8 * sizeof(double)));
 	// the state this step starts from, whole (every rank holds all positions)
 	if ((rc = ensure_y_gathered(ctx))) return rc;
 	CK(cudaMemcpyAsync(ctx->undo_Y, ctx->Y, (size_t)ctx->n_pad * v4, cudaMemcpyDeviceToDevice, ctx->sc));
@@ -1652,9 +1826,13 @@ int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out) {
 	ctx->tm.pair_symmetry = sym_in_use(ctx) ? 1u : 0u;
 	ctx->tm.graph_captures = ctx->graph_captures;
 	ctx->tm.sym_variant = 0;
+	ctx->tm.deterministic = sym_in_use(ctx) ? 0u : 1u;	// the one-sided kernel sums in a fixed order
+	ctx->tm.reserved0 = 0;
 	if (sym_in_use(ctx)) {
 		const SymVariant* tab = ctx->prec == 64 ? g_sym64 : g_sym32;
-		ctx->tm.sym_variant = (uint32_t)(&sym_variant_of(ctx) - tab);
+		const SymVariant& sv = sym_variant_of(ctx);
+		ctx->tm.sym_variant = (uint32_t)(&sv - tab);
+		ctx->tm.deterministic = sv.fx ? 1u : 0u;
 	}
 	{
 		const int nv = ctx->prec == 64 ? N_VAR64 : N_VAR32;

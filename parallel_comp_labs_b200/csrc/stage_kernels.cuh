@@ -14,6 +14,7 @@
 #endif
 #include <stdint.h>
 
+#include "fixed_sums.cuh"
 #include "force_kernels.cuh"
 
 namespace nbody {
@@ -37,6 +38,8 @@ struct StageParams {
 	unsigned apart_stride;	// rows between consecutive slices of apart (own_pad for K1)
 	const void* aj;			// optional T[3][aj_stride]: j-side sums of the pair-symmetric kernel
 	unsigned aj_stride;
+	int aj_fx, aj_e0;		// aj_fx != 0: aj holds fixed-point sums, uint64[FX_PLANES][aj_stride] with the
+							// lowest bit worth 2^aj_e0 (option "deterministic", fixed_sums.cuh)
 	T mass_scale;	 // the uniform mass factored out of K1 (1 when masses differ: exact no-op)
 	T minusG;		 // -G
 	T c_next;		 // a_{s+1,s} * tau (tau/2, tau/2, tau for RK4; tau/2 for RK2)
@@ -44,6 +47,30 @@ struct StageParams {
 	T final_scale;	 // tau/6 (RK4) or tau (RK2)
 	int first, last;
 };
+
+// raw sums of row `own0 + i` collected by force_sym_kernel: floating-point (RED) or fixed-point
+template <typename T>
+__device__ __forceinline__ void read_row_sums(const StageParams<T>& p, const unsigned i, T& ax,
+											   T& ay, T& az) {
+	if (p.aj_fx) {
+		const unsigned long long* planes =
+			reinterpret_cast<const unsigned long long*>(p.aj) + (size_t)p.own0 + i;
+		const size_t st = p.aj_stride;
+		if (planes[(size_t)(3 * FX_LIMBS) * st]) {	// a non-finite contribution reached this row
+			const T nan = (T)__longlong_as_double(0x7ff8000000000000ll);
+			ax = ay = az = nan;
+			return;
+		}
+		ax = add_rn(ax, (T)fx_read(planes, st, p.aj_e0));
+		ay = add_rn(ay, (T)fx_read(planes + (size_t)FX_LIMBS * st, st, p.aj_e0));
+		az = add_rn(az, (T)fx_read(planes + (size_t)(2 * FX_LIMBS) * st, st, p.aj_e0));
+		return;
+	}
+	const T* g = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
+	ax = add_rn(ax, g[0]);
+	ay = add_rn(ay, g[(size_t)p.aj_stride]);
+	az = add_rn(az, g[2 * (size_t)p.aj_stride]);
+}
 
 template <typename T>
 __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
@@ -59,12 +86,7 @@ __global__ void __launch_bounds__(256) stage_kernel(const StageParams<T> p) {
 		ay = add_rn(ay, q.y);
 		az = add_rn(az, q.z);
 	}
-	if (p.aj) {	 // reactions collected by force_sym_kernel (global row index)
-		const T* g = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
-		ax = add_rn(ax, g[0]);
-		ay = add_rn(ay, g[(size_t)p.aj_stride]);
-		az = add_rn(az, g[2 * (size_t)p.aj_stride]);
-	}
+	if (p.aj) read_row_sums<T>(p, i, ax, ay, az);  // collected by force_sym_kernel (global row index)
 	ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
 	ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
 	az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);
@@ -178,12 +200,7 @@ __global__ void __launch_bounds__(256) stage_general_kernel(const StageGenParams
 				ay = add_rn(ay, q.y);
 				az = add_rn(az, q.z);
 			}
-			if (p.aj) {
-				const T* gj = reinterpret_cast<const T*>(p.aj) + (size_t)p.own0 + i;
-				ax = add_rn(ax, gj[0]);
-				ay = add_rn(ay, gj[(size_t)p.aj_stride]);
-				az = add_rn(az, gj[2 * (size_t)p.aj_stride]);
-			}
+			if (p.aj) read_row_sums<T>(p, i, ax, ay, az);
 			ax = mul_rn(mul_rn(ax, p.mass_scale), p.minusG);
 			ay = mul_rn(mul_rn(ay, p.mass_scale), p.minusG);
 			az = mul_rn(mul_rn(az, p.mass_scale), p.minusG);

@@ -494,3 +494,109 @@ def test_emulated_trace_lists_every_operation_of_a_step():
     kinds = [t["kind"] for t in tr]
     assert kinds.count("force") == 4 and kinds.count("stage") == 4 and kinds.count("memset") == 4
     assert all(t["dur_ms"] >= 0 and t["stream"] == "compute" for t in tr)
+
+
+# ------------------------------------------------------------------ option "deterministic"
+class _cta_order:
+    """Run the emulated CTAs of every launch in a pseudo-random order (tests/tools/cuda_emu.h,
+    EMU_CTA_SHUFFLE): with the ticket-counter kernels that changes which CTA takes which unit and
+    the order in which the units' sums reach global memory -- the freedom a GPU's scheduler has."""
+
+    def __init__(self, seed):
+        self.seed = seed
+
+    def __enter__(self):
+        if self.seed is None:
+            os.environ.pop("EMU_CTA_SHUFFLE", None)
+        else:
+            os.environ["EMU_CTA_SHUFFLE"] = str(self.seed)
+
+    def __exit__(self, *exc):
+        os.environ.pop("EMU_CTA_SHUFFLE", None)
+
+
+@pytest.mark.parametrize("prec,general", [(64, False), (64, True), (32, False)])
+def test_emulated_deterministic_row_sums_do_not_depend_on_unit_order(oracle, prec, general):
+    """Option "deterministic" (fixed-point row sums, csrc/fixed_sums.cuh): same tolerances against
+    the oracle as the floating-point sums, and the SAME BITS whatever order the units finish in --
+    while the floating-point RED sums of the default mode do change with it."""
+    b = generators.plummer_bodies(1100, seed=29)
+    b[7, 1:4] = b[8, 1:4] + 1e-5                       # a pair inside the clamp radius
+    b[900, 1:4] = b[20, 1:4]                           # a coincident pair in different blocks
+    if general:
+        b[:, 0] *= np.linspace(0.5, 2.0, b.shape[0])
+        b[33, 0] = 0.0
+    bb = b.astype(np.float32 if prec == 32 else np.float64)
+    want = oracle.rhs(bb.astype(np.float64), eps=1e-3, threads=8)[:, 4:7]
+    tol = 1e-12 if prec == 64 else 1e-4
+    runs = {}
+    for det in (0, 1):
+        for seed in (None, 1, 2):
+            with _cta_order(seed):
+                got, tm = run_rhs(bb, prec=prec, eps=1e-3, pair_symmetry=1, slices=3, deterministic=det)
+            assert tm.pair_symmetry == 1 and tm.deterministic == det
+            assert tm.uniform_mass == (0 if general else 1)
+            assert rel_inf(got, want) < tol
+            runs[det, seed] = got
+    for seed in (1, 2):
+        assert np.array_equal(runs[1, None], runs[1, seed])
+    assert any(not np.array_equal(runs[0, None], runs[0, seed]) for seed in (1, 2))
+    assert rel_inf(runs[1, None], runs[0, None]) < (1e-14 if prec == 64 else 1e-5)
+
+
+def test_emulated_deterministic_steps_graph_errors_and_reporting(oracle, golden):
+    b = generators.uniform_bodies(640, seed=31)        # general masses, eps = 1e-6: the reference's regime
+    want, _ = oracle.rk4(b, 0.1, 0.0, 1.0, eps=1e-6, max_steps=2, rows=False, threads=8)
+    outs = []
+    for seed, graph in ((None, 0), (5, 0), (6, 1), (None, 1)):
+        with _cta_order(seed):
+            outs.append(run_steps(b, capi.NBODY_RK4, 0.1, 2, eps=1e-6, pair_symmetry=1, deterministic=1,
+                                  use_graph=graph))
+        check_state(outs[-1], want, b, 1e-10)
+    for o in outs[1:]:
+        assert np.array_equal(outs[0], o)              # replayed graph or not, any unit order: same bits
+    # the one-sided kernel sums in a fixed order: it reports deterministic without the option
+    _, tm = run_rhs(b, pair_symmetry=0)
+    assert tm.deterministic == 1 and tm.pair_symmetry == 0
+    # eps = 0: no bound on a contribution -> refused, loudly (the floating-point mode returns the
+    # reference's NaNs there)
+    with pytest.raises(capi.NBodyError):
+        run_rhs(b, eps=0.0, pair_symmetry=1, deterministic=1)
+    # the window is derived from the uploaded bodies: the option must precede the upload
+    with capi.Context(b.shape[0], 64) as ctx:
+        ctx.set_option("pair_symmetry", 1)
+        ctx.upload_aos(b)
+        with pytest.raises(capi.NBodyError):
+            ctx.set_option("deterministic", 1)
+        ctx.rhs()                                      # still usable in the default mode
+    # a non-finite contribution poisons exactly the rows the floating-point sums make non-finite
+    bad = b.copy()
+    bad[100, 1] = np.nan
+    got_f, _ = run_rhs(bad, pair_symmetry=1)
+    got_d, _ = run_rhs(bad, pair_symmetry=1, deterministic=1)
+    assert np.array_equal(np.isnan(got_f).any(axis=1), np.isnan(got_d).any(axis=1))
+    # a dynamic range the 192-bit window cannot hold (eps far below anything the positions resolve)
+    with pytest.raises(capi.NBodyError):
+        run_rhs(b, eps=1e-40, pair_symmetry=1, deterministic=1)
+
+
+@pytest.mark.parametrize("world,owned_io", [(2, False), (3, True)])
+def test_emulated_deterministic_on_several_ranks(oracle, world, owned_io):
+    """The fixed-point limbs are reduce-scattered as integers: every rank against the oracle, and the
+    same bits for any unit order on any rank (owned_io: the window's input statistics are
+    all-reduced with the equal-mass test of nbody_upload_aos_owned)."""
+    n = 800
+    b = generators.plummer_bodies(n, seed=17)
+    b[:, 0] *= np.linspace(0.7, 1.4, n)
+    want, _ = oracle.rk4(b, 1e-3, 0.0, 1.0, eps=1e-3, max_steps=2, rows=False, threads=8)
+    base = None
+    for seed in (None, 4):
+        with _cta_order(seed):
+            res = _run_ranks(world, b, 1e-3, 1e-3, 2, owned_io=owned_io, pair_symmetry=1, deterministic=1)
+        for o in res:
+            assert o["tm"].deterministic == 1 and o["tm"].pair_symmetry == 1
+            check_state(o["fin"], want, b, 1e-10)
+            assert np.array_equal(o["fin"], res[0]["fin"])
+        if base is None:
+            base = res[0]["fin"]
+        assert np.array_equal(base, res[0]["fin"])

@@ -147,7 +147,21 @@ inline void launch(dim3 grid, dim3 block, size_t smem_bytes, const std::function
 	if (block.x % 32 || block.y != 1 || block.z != 1) throw std::runtime_error("emu: block must be (32k,1,1)");
 	Entry e{kernel};
 	entry() = &e;
-	for (unsigned b = 0; b < grid.x; ++b) {
+	// EMU_CTA_SHUFFLE=<seed> (read at every launch): run the CTAs in a pseudo-random order instead
+	// of 0,1,2,...  With persistent kernels that draw work from a ticket counter this changes which
+	// CTA takes which unit and the ORDER in which units reach global memory -- the emulated
+	// counterpart of the GPU's scheduling freedom (used to show that the fixed-point row sums of
+	// option "deterministic" do not depend on it while the floating-point ones do).
+	std::vector<unsigned> cta_order(grid.x);
+	for (unsigned b = 0; b < grid.x; ++b) cta_order[b] = b;
+	if (const char* e = getenv("EMU_CTA_SHUFFLE")) {
+		uint64_t x = (uint64_t)strtoull(e, nullptr, 0) * 0x9E3779B97F4A7C15ull + 1;
+		for (size_t t = cta_order.size(); t > 1; --t) {
+			x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+			std::swap(cta_order[t - 1], cta_order[(size_t)(x % t)]);
+		}
+	}
+	for (unsigned b : cta_order) {
 		Cta c;
 		c.block_idx = dim3(b);
 		c.block_dim = block;
@@ -255,6 +269,9 @@ inline long long __double_as_longlong(double x) { long long v; memcpy(&v, &x, 8)
 inline double __longlong_as_double(long long v) { double x; memcpy(&x, &v, 8); return x; }
 inline int __double2hiint(double x) { return (int)(__double_as_longlong(x) >> 32); }
 inline int __float_as_int(float x) { int v; memcpy(&v, &x, 4); return v; }
+inline int __clz(int x) { return x == 0 ? 32 : __builtin_clz((unsigned)x); }
+inline double __ull2double_rn(unsigned long long v) { return (double)v; }  // round to nearest even
+using std::ldexp;
 inline double rsqrt(double x) { return 1.0 / std::sqrt(x); }
 using std::fma;
 using std::max;

@@ -38,7 +38,7 @@ std::mutex g_mu;
 std::map<uint64_t, Group*> g_groups;
 uint64_t g_next_id = 1;
 
-size_t elem_size(int dt) { return dt == 8 ? 8 : dt == 7 ? 4 : 1; }
+size_t elem_size(int dt) { return (dt == 8 || dt == 5) ? 8 : dt == 7 ? 4 : 1; }  // ncclUint64 = 5
 
 template <typename T>
 void sum_into(T* out, const std::vector<const void*>& send, size_t offset, size_t count, int op = 0) {
@@ -125,13 +125,14 @@ int ncclAllReduce(const void* send, void* recv, size_t count, int dt, int op, nc
 }
 
 int ncclReduceScatter(const void* send, void* recv, size_t recvcount, int dt, int op, ncclComm_t c, void*) {
-	if (op != 0 || (dt != 8 && dt != 7)) return 4;
+	if (op != 0 || (dt != 8 && dt != 7 && dt != 5)) return 4;
 	Group* g = c->g;
 	g->send[c->rank] = send;
 	g->barrier();
 	std::vector<char> tmp(recvcount * elem_size(dt));
 	const size_t off = (size_t)c->rank * recvcount;
 	if (dt == 8) sum_into(reinterpret_cast<double*>(tmp.data()), g->send, off, recvcount);
+	else if (dt == 5) sum_into(reinterpret_cast<uint64_t*>(tmp.data()), g->send, off, recvcount);
 	else sum_into(reinterpret_cast<float*>(tmp.data()), g->send, off, recvcount);
 	g->barrier();
 	memcpy(recv, tmp.data(), tmp.size());
