@@ -54,6 +54,9 @@ def parse():
                          "0: the one-sided kernel (every ordered pair, as the reference does; "
                          "bit-reproducible)")
     ap.add_argument("--sym-variant", type=int, default=-1)
+    ap.add_argument("--deterministic", type=int, default=0,
+                    help="1: the pair-symmetric kernel with fixed-point row sums (bit-reproducible "
+                         "whatever the scheduling); 0 (default): floating-point RED sums")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-energy", action="store_true")
     ap.add_argument("--trace-out", default="",
@@ -306,6 +309,7 @@ def run_b200(args):
     ctx.set_option("unimass", args.unimass)
     ctx.set_option("pair_symmetry", args.pair_symmetry)
     ctx.set_option("sym_variant", args.sym_variant)
+    ctx.set_option("deterministic", args.deterministic)
     host_in = capi.PinnedArray((n, 7), dtype)
     host_out = capi.PinnedArray((n, 7), dtype)
     host_in.array[:] = bodies.astype(dtype)
@@ -433,6 +437,35 @@ def run_b200(args):
                 "uniform_mass_factored_out": bool(t2.uniform_mass),
                 "pair_symmetry": bool(t2.pair_symmetry),
                 "note": "same bodies, option unimass=0: the kernels any input with distinct masses gets"}}
+    # ---- secondary figure: the bit-reproducible mode of the pair-symmetric kernel (one GPU) -----
+    # option "deterministic": fixed-point row sums.  Two RHS evaluations must agree bit for bit.
+    if (not args.no_secondary and world == 1 and tm.pair_symmetry and not args.deterministic):
+        try:
+            with capi.Context(n, args.precision, local, rank, world, None) as c3:
+                c3.set_params(6.67e-11, eps)
+                c3.set_option("unimass", args.unimass)
+                c3.set_option("pair_symmetry", args.pair_symmetry)
+                c3.set_option("deterministic", 1)
+                c3.upload_aos(host_in.array)
+                r1 = c3.rhs()
+                r2 = c3.rhs()
+                c3.step(scheme, tau, 1)
+                c3.sync()
+                ms3 = []
+                for _ in range(2):
+                    c3.step(scheme, tau, 1)
+                    c3.sync()
+                    ms3.append(c3.timing().last_call_ms)
+                t3 = c3.timing()
+                det = {"value": stages * float(n) * float(n) * 2 / (sum(ms3) * 1e-3) / 1e9,
+                       "unit": "G interactions/s", "steps": 2, "warmup": 1,
+                       "deterministic": bool(t3.deterministic), "sym_variant": int(t3.sym_variant),
+                       "two_rhs_bitwise_equal": bool(np.array_equal(r1, r2)),
+                       "note": "option deterministic=1: every unit's share of a row is added as an exact "
+                               "fixed-point integer (64-bit integer RED) instead of a floating-point RED"}
+        except capi.NBodyError as ex:
+            det = {"error": str(ex)}
+        secondary = dict(secondary or {}, deterministic=det)
     total_launches = int(sum_over_ranks(float(launches)))
     sum_pairs = sum_over_ranks(float(pair_evals))
 
@@ -448,6 +481,7 @@ def run_b200(args):
             # instructions per evaluation; `value` and roofline.achieved count DELIVERED
             # interactions (the metric's definition), roofline.evaluated_* what was computed
             variant_name.update({"pair_symmetry": True, "sym_variant": int(tm.sym_variant),
+                                 "deterministic_row_sums": bool(tm.deterministic),
                                  "fp64_instr_per_pair": None,
                                  "fp64_instr_per_pair_evaluation":
                                      (18 if tm.uniform_mass else 20) if args.precision == 64 else None})

@@ -352,6 +352,7 @@ struct RunOptions {
 	double adaptive_rtol = 0;  // > 0: step-size control over the embedded pair `tableau`, tau = first step
 	double adaptive_atol = 0;
 	long pair_symmetry = -1;  // -1 auto (library default), 0 one-sided bit-reproducible kernel, 1 pair-symmetric
+	long deterministic = 0;	  // 1: fixed-point row sums in the pair-symmetric kernel (bit-reproducible)
 	bool report = false;
 };
 
@@ -441,6 +442,7 @@ class Solver_N_body {
 		if (nbody_set_params(ctx, (double)sys.G, (double)sys.eps)) return fail("set_params");
 		if (opt.variant >= 0 && nbody_set_option(ctx, "variant", opt.variant)) return fail("variant");
 		if (nbody_set_option(ctx, "pair_symmetry", opt.pair_symmetry)) return fail("pair_symmetry");
+		if (nbody_set_option(ctx, "deterministic", opt.deterministic)) return fail("deterministic");
 		if (nbody_upload_aos(ctx, sys.traj_init.data())) return fail("upload");
 
 		std::ofstream traj;

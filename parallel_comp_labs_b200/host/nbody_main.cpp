@@ -46,7 +46,7 @@ void usage() {
 		"           [--adaptive-rtol R [--adaptive-atol A]]   (step-size control, embedded pairs; --tau = first step)\n"
 		"           [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
-		"           [--output-folder ../output] [--variant -1] [--pair-symmetry [0|1]] [--report]\n"
+		"           [--output-folder ../output] [--variant -1] [--pair-symmetry [0|1]] [--deterministic] [--report]\n"
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
 		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
 		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)\n"
@@ -99,6 +99,8 @@ int run(const Args& a) {
 	// --pair-symmetry [0|1]: 1 (or bare flag) forces the pair-symmetric kernel, 0 the one-sided
 	// bit-reproducible kernel; absent = the library's automatic choice
 	opt.pair_symmetry = a.has("pair-symmetry") ? (a.str("pair-symmetry", "1") == "0" ? 0 : 1) : -1;
+	// --deterministic: fixed-point row sums in the pair-symmetric kernel (same bits every run)
+	opt.deterministic = a.has("deterministic") ? (a.str("deterministic", "1") == "0" ? 0 : 1) : 0;
 	opt.report = a.has("report");
 
 	Solver_N_body<T> solver;

@@ -50,7 +50,7 @@ def test_deterministic_rhs_same_bits_every_run_and_within_tolerance(oracle, n, p
     assert per_row(det[0][rows], want) < (1e-10 if prec == 64 else 2e-3)
     flt, tmf = rhs(bb, prec, pair_symmetry=1)
     assert tmf.deterministic == 0
-    assert rel_inf(det[0], flt[0]) < (1e-13 if prec == 64 else 1e-5)
+    assert rel_inf(det[0], flt[0]) < (2e-13 if prec == 64 else 1e-4)
 
 
 def test_deterministic_every_fixed_point_build(oracle):
