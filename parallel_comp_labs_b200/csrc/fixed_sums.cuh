@@ -30,10 +30,17 @@ constexpr int FX_LIMBS = 6;					// 192-bit window
 constexpr int FX_PLANES = 3 * FX_LIMBS + 1;	// x, y, z limbs + one poison word per row
 constexpr int FX_WINDOW_BITS = 32 * FX_LIMBS;
 
-// planes[(c * FX_LIMBS + k) * stride + row], poison = planes[3 * FX_LIMBS * stride + row]
-__device__ __forceinline__ void fx_add(unsigned long long* __restrict__ limb0, const size_t stride,
-									   unsigned long long* __restrict__ poison, const double x,
-									   const int e0) {
+// The host keeps |e0| <= FX_E0_LIMIT (nbody_capi.cu: fx_window refuses anything else), so that in
+// fx_add a zero / subnormal (biased exponent 0) lands below the window and inf / NaN (0x7ff) above
+// the fast path's range without separate tests.
+constexpr int FX_E0_LIMIT = 800;
+
+// Anything the fast path of fx_add does not take: zero, bits below the window (dropped towards
+// zero), inf / NaN and values at the top of the window (poison).
+__device__ __forceinline__ void fx_add_slow(unsigned long long* __restrict__ limb0,
+											const size_t stride,
+											unsigned long long* __restrict__ poison, const double x,
+											const int e0) {
 	const unsigned long long b = (unsigned long long)__double_as_longlong(x);
 	const int ex = (int)((b >> 52) & 0x7ffu);
 	if (ex == 0) return;  // zero (and subnormals: far below any window in use)
@@ -64,6 +71,31 @@ __device__ __forceinline__ void fx_add(unsigned long long* __restrict__ limb0, c
 	if (c0) atomicAdd(limb0 + (size_t)k * stride, c0);
 	if (c1) atomicAdd(limb0 + (size_t)(k + 1) * stride, c1);
 	if (c2) atomicAdd(limb0 + (size_t)(k + 2) * stride, c2);
+}
+
+// planes[(c * FX_LIMBS + k) * stride + row], poison = planes[3 * FX_LIMBS * stride + row]
+// Fast path (a normal number whose 53 bits lie inside the window with two limbs to spare): the
+// 53-bit mantissa shifted by r = p mod 32 IS three 32-bit words -- three funnel shifts -- each
+// added to (subtracted from) its limb with one 64-bit integer RED; zero words are skipped.
+__device__ __forceinline__ void fx_add(unsigned long long* __restrict__ limb0, const size_t stride,
+									   unsigned long long* __restrict__ poison, const double x,
+									   const int e0) {
+	const unsigned hi = (unsigned)__double2hiint(x), lo = (unsigned)__double2loint(x);
+	const int p = (int)((hi >> 20) & 0x7ffu) - 1075 - e0;  // position of the lowest mantissa bit
+	if ((unsigned)p >= (unsigned)(32 * (FX_LIMBS - 2))) {
+		fx_add_slow(limb0, stride, poison, x, e0);
+		return;
+	}
+	const unsigned mh = (hi & 0xfffffu) | 0x100000u;
+	const int r = p & 31;
+	const unsigned c0 = lo << r;
+	const unsigned c1 = __funnelshift_l(lo, mh, r);
+	const unsigned c2 = __funnelshift_l(mh, 0u, r);
+	const bool neg = (int)hi < 0;
+	unsigned long long* q = limb0 + (size_t)(p >> 5) * stride;
+	if (c0) atomicAdd(q, neg ? 0ull - (unsigned long long)c0 : (unsigned long long)c0);
+	if (c1) atomicAdd(q + stride, neg ? 0ull - (unsigned long long)c1 : (unsigned long long)c1);
+	if (c2) atomicAdd(q + 2 * stride, neg ? 0ull - (unsigned long long)c2 : (unsigned long long)c2);
 }
 
 // The double nearest to the limbs' value (round to nearest even, one rounding).

@@ -398,6 +398,11 @@ int fx_window(const nbody_ctx* c, int* e0, std::string* why) {
 	std::frexp((double)c->n, &ex);
 	top += ex + 2;
 	*e0 = top - FX_WINDOW_BITS;
+	if (*e0 < -FX_E0_LIMIT || *e0 > FX_E0_LIMIT) {	// fixed_sums.cuh: fx_add relies on it
+		*why = "option \"deterministic\": n m_max / eps^2 = 2^" + std::to_string(top) +
+			   " is outside the range the fixed-point sums are built for";
+		return NBODY_ERR_STATE;
+	}
 	if (c->coord_absmax > 0. && mmin > 0.) {
 		int em = 0, ed = 0;
 		std::frexp(mmin, &em);					 // mmin >= 2^(em-1)

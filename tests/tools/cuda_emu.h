@@ -269,6 +269,12 @@ inline long long __double_as_longlong(double x) { long long v; memcpy(&v, &x, 8)
 inline double __longlong_as_double(long long v) { double x; memcpy(&x, &v, 8); return x; }
 inline int __double2hiint(double x) { return (int)(__double_as_longlong(x) >> 32); }
 inline int __float_as_int(float x) { int v; memcpy(&v, &x, 4); return v; }
+inline int __double2loint(double x) { return (int)(unsigned)(__double_as_longlong(x) & 0xffffffffLL); }
+// upper 32 bits of (hi:lo) << (shift & 31)
+inline unsigned __funnelshift_l(unsigned lo, unsigned hi, unsigned shift) {
+	const unsigned s = shift & 31u;
+	return s ? (hi << s) | (lo >> (32u - s)) : hi;
+}
 inline int __clz(int x) { return x == 0 ? 32 : __builtin_clz((unsigned)x); }
 inline double __ull2double_rn(unsigned long long v) { return (double)v; }  // round to nearest even
 using std::ldexp;

@@ -24,7 +24,10 @@ P2P = os.environ.get("NBODY_P2P", "0") == "1"
 # NBODY_PAIR_SYM: "1" pair-symmetric kernel + reduce-scatter, "0" one-sided kernel (all-gather
 # overlapped with the local-tile launch), unset / "auto" = the library's choice
 SYM_OPT = {"0": 0, "1": 1}.get(os.environ.get("NBODY_PAIR_SYM", "auto"), -1)
-PAIR_SYM = SYM_OPT != 0   # tolerance class of the owned-rows comparison (atomics: rounding only)
+# NBODY_DETERMINISTIC=1: option "deterministic" (fixed-point row sums, integer reduce-scatter): the
+# runs must then agree BIT FOR BIT where the floating-point sums agree to rounding
+DET = os.environ.get("NBODY_DETERMINISTIC", "0") == "1"
+PAIR_SYM = SYM_OPT != 0 and not DET  # tolerance class of the owned-rows comparison (atomics: rounding only)
 o = Oracle()
 ok = True
 for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1e-6, 0.1),
@@ -38,14 +41,19 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
                 ctx.p2p_connect(blobs)
             ctx.set_params(6.67e-11, eps)
             ctx.set_option("pair_symmetry", SYM_OPT)
+            ctx.set_option("deterministic", 1 if DET else 0)
             ctx.upload_aos(bodies)
             b, e = ctx.owned_range()
             a = ctx.rhs().astype(np.float64)
+            a_again = ctx.rhs().astype(np.float64) if DET else None
             want = o.rhs(bodies, b, e, eps=eps, threads=4)[b:e, 4:7]
             full = o.rhs(bodies, eps=eps, threads=4)[:, 4:7] if rank == 0 and nn <= 20000 else None
             err = np.abs(a[b:e] - want).max() / max(np.abs(want).max(), 1e-300) if e > b else 0.0
             assert np.all(np.isnan(a[:b])) and np.all(np.isnan(a[e:]))
             res = {"rhs": err, "sym": float(ctx.timing().pair_symmetry)}
+            if DET:
+                assert ctx.timing().deterministic == 1
+                res["det_bits_differ"] = 0.0 if np.array_equal(a[b:e], a_again[b:e]) else 1.0
             for scheme, fn in ((2, o.rk2), (4, o.rk4)):
                 ctx.upload_aos(bodies)
                 ctx.step(scheme, tau, 3)
@@ -82,7 +90,7 @@ for (name, bodies, eps, tau) in (("uniform", generators.uniform_bodies(n, 31), 1
                 w2, _ = o.rk_general(bodies, tb["a"], tb["b"], tau, 1, eps=eps, threads=4)
                 res["emb_r"] = float(np.abs(fin[:, 1:4] - w2[:, 1:4]).max() / np.abs(w2[:, 1:4]).max())
             lim = {"rhs": tol, "_r": tol, "_dv": max(tol * 10, dv_floor), "emb_norms": 1e-4, "_snap": 0.0 if prec == 64 else 1e-6,
-                   "_E": max(tol * 10, 1e-9), "_owned": tol if PAIR_SYM else 0.0}
+                   "_E": max(tol * 10, 1e-9), "_owned": tol if PAIR_SYM else 0.0, "det_bits_differ": 0.0}
             good = all(v <= next(l for suf, l in lim.items() if k_.endswith(suf))
                        for k_, v in res.items() if k_ != "sym")
             ok &= good
@@ -97,4 +105,5 @@ if flag.item():
     print("MULTI-GPU CHECK FAILED"); sys.exit(1)
 if rank == 0:
     print("MULTI-GPU CHECK PASSED" + (" (peer-pull exchange)" if P2P else " (NCCL all-gather)")
-          + {0: " (one-sided kernel)", 1: " (pair-symmetric kernel)", -1: " (automatic kernel choice)"}[SYM_OPT])
+          + {0: " (one-sided kernel)", 1: " (pair-symmetric kernel)", -1: " (automatic kernel choice)"}[SYM_OPT]
+          + (" (deterministic: fixed-point row sums)" if DET else ""))

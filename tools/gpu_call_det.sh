@@ -5,7 +5,7 @@
 #   gpurun --timeout 600 -- 'bash tools/gpu_call_det.sh'
 set -u
 cd "$(dirname "$0")/.."
-OUT=gpurun_out/det
+OUT=${OUT:-gpurun_out/det2}
 mkdir -p "$OUT"
 PY=python
 DEADLINE=${DEADLINE:-510}	# seconds of wall clock this script may use in all (GPU budget)
@@ -16,8 +16,8 @@ step() { local name=$1 secs=$2; shift 2; echo "== $name" | tee -a "$OUT/summary.
 	timeout "$secs" "$@" > "$OUT/$name.log" 2>&1; local rc=$?; echo "   exit $rc  ($((SECONDS - t0)) s)" | tee -a "$OUT/summary.txt"; return $rc; }
 bench_line() { local name=$1 secs=$2; shift 2
 	step "$name" "$secs" $PY bench.py "$@" && grep '^{' "$OUT/$name.log" | tail -1 > "$OUT/$name.json"; }
-step pytest_det 240 $PY -m pytest tests/test_zzz_gpu_deterministic.py -m gpu -q -x
-bench_line bench_default 240 --steps 2 --warmup 3 --cpu-seconds 4
+step pytest_gpu 400 $PY -m pytest tests -m gpu -q -x
+step smoke 60 $PY -c "import __graft_entry__ as g; g.smoke()"
 bench_line bench_det_1m 120 --deterministic 1 --steps 2 --warmup 3 --no-cpu-baseline --no-secondary --no-energy
 bench_line bench_det_general_1m 120 --deterministic 1 --unimass 0 --steps 2 --warmup 2 --no-cpu-baseline --no-secondary --no-energy
 bench_line bench_det_256k 60 --deterministic 1 --bodies 262144 --steps 5 --warmup 3 --no-cpu-baseline --no-secondary --no-energy
@@ -29,6 +29,5 @@ step ncu_det_256k 150 ncu --set full --clock-control none --import-source on -k 
 	--no-cpu-baseline --no-secondary --no-energy --no-parity
 [ -f "$OUT/k1s_fx_fp64_equal_262144.ncu-rep" ] && $PY tools/ncu_summary.py "$OUT/k1s_fx_fp64_equal_262144.ncu-rep" \
 	"$OUT/ncu_k1s_fx_fp64_equal_262144.csv" > /dev/null 2>&1
-step pytest_gpu 400 $PY -m pytest tests -m gpu -q -x
-step smoke 60 $PY -c "import __graft_entry__ as g; g.smoke()"
+bench_line bench_default 240 --steps 2 --warmup 3 --cpu-seconds 4
 cat "$OUT/summary.txt"

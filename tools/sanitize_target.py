@@ -35,6 +35,7 @@ for n in sizes:
                         ctx.set_option("sym_variant", s)
                     except capi.NBodyError:
                         break
+                    ctx.upload_aos(bodies)                # the fixed-point builds take their window from the upload
                     ctx.rhs()
                     s += 1
                 ctx.set_option("sym_variant", -1)
