@@ -38,6 +38,20 @@ def test_two_ranks_match_oracle(p2p, sym, port):
 
 
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs >= 2 GPUs")
+def test_two_ranks_deterministic_row_sums():
+    """Option "deterministic" on two ranks: the fixed-point limbs are reduce-scattered as 64-bit
+    integers; every rank against the oracle, repeated evaluations and the owned-rows upload path
+    must give the same BITS (tests/tools/multi_check.py, NBODY_DETERMINISTIC=1)."""
+    env = dict(os.environ, NBODY_P2P="0", NBODY_PAIR_SYM="auto", NBODY_DETERMINISTIC="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                        "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port",
+                        "29537", os.path.join(ROOT, "tests", "tools", "multi_check.py"), "3000"],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "deterministic: fixed-point row sums" in r.stdout, \
+        r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs >= 2 GPUs")
 def test_cxx_driver_two_gpus_matches_one(tmp_path):
     """The C++ host driver with one rank-thread per GPU (NCCL from threads of one process)."""
     import numpy as np
