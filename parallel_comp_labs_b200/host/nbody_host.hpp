@@ -266,6 +266,167 @@ struct ode_system {
 	}
 };
 
+// ---- where a trajectory row goes ---------------------------------------------------------------
+// One row = (time, n x 3 positions).  Three independent outputs:
+//  * the whole-system CSV of the reference, "t;x1;y1;z1;...;zN;" (write_bodies_coords,
+//    read_write_utils.hpp:42-52) -- byte-compatible, 72 MB per row at N = 1M;
+//  * a binary sidecar: 32-byte header {"NBTRJ01", n, sizeof(T), flavour} + per row {double t,
+//    T pos[3n]} -- what a long run at large N should write (3n sizeof(T) bytes per row instead of
+//    72 n characters); `nbody_b200 --bin2csv` / `--bin2perbody` turn it into the text formats
+//    afterwards, byte-identical to what a direct run writes;
+//  * per-body files traj<k>.csv, k = 1..: "time;r1;r2;r3" then "t;x;y;z" per row -- the layout of the
+//    reference's own fixtures (N_body_config/traj1.csv:1), for diffing body by body.
+constexpr std::size_t MAX_PER_BODY_FILES = 256;	 // open at once (fd limit); select a range above that
+
+struct TrajBinHeader {
+	char magic[8];		 // "NBTRJ01\0"
+	std::uint64_t n;	 // bodies per row
+	std::uint32_t elem;	 // sizeof(T): 8 or 4
+	std::uint32_t flavour;	// 4 = lab_4 (4-body header, t_start row), 5 = lab_5 (N-body header)
+	std::uint64_t reserved;
+};
+static_assert(sizeof(TrajBinHeader) == 32, "binary trajectory header is 32 bytes");
+
+inline void append_sci16_bare(std::string& s, double x) {
+	char buf[40];
+	auto res = std::to_chars(buf, buf + sizeof(buf), x, std::chars_format::scientific, 16);
+	s.append(buf, res.ptr);
+}
+
+struct PerBodyFiles {
+	std::vector<std::ofstream> files;
+	std::size_t first = 0;	// 0-based index of the body traj<first+1>.csv follows
+	// opens DIR/traj<k>.csv for bodies [first, first + count); false (with `why`) on failure
+	bool open(const std::string& dir, std::size_t n, std::size_t first_body, std::size_t count,
+			  std::string* why) {
+		if (first_body >= n) { *why = "--per-body-first is past the last body"; return false; }
+		if (count == 0 || first_body + count > n) count = n - first_body;
+		if (count > MAX_PER_BODY_FILES) {
+			*why = "per-body trajectory files: " + std::to_string(count) + " bodies selected, at most " +
+				   std::to_string(MAX_PER_BODY_FILES) + " files are kept open at once; narrow the range "
+				   "with --per-body-first / --per-body-count (or write --traj-bin and convert ranges "
+				   "with --bin2perbody afterwards)";
+			return false;
+		}
+		first = first_body;
+		files.resize(count);
+		for (std::size_t k = 0; k < count; ++k) {
+			const std::string path = dir + "/traj" + std::to_string(first + k + 1) + ".csv";
+			files[k].open(path);
+			if (!files[k].is_open()) { *why = "cannot open " + path; return false; }
+			files[k] << "time;r1;r2;r3\n";	 // N_body_config/traj1.csv:1
+		}
+		return true;
+	}
+	template <typename T>
+	void row(double time, const T* pos) {
+		std::string line;
+		for (std::size_t k = 0; k < files.size(); ++k) {
+			line.clear();
+			append_sci16(line, time);
+			const T* p = pos + 3 * (first + k);
+			append_sci16(line, (double)p[0]);
+			append_sci16(line, (double)p[1]);
+			append_sci16_bare(line, (double)p[2]);
+			line.push_back('\n');
+			files[k].write(line.data(), (std::streamsize)line.size());
+		}
+	}
+	void flush() { for (auto& f : files) f.flush(); }
+};
+
+template <typename T>
+struct TrajectorySinks {
+	std::ostream* csv = nullptr;   // whole-system CSV (header already written by the caller)
+	std::ofstream bin;			   // binary sidecar
+	PerBodyFiles per_body;
+	std::size_t n = 0;
+	bool any() const { return csv || bin.is_open() || !per_body.files.empty(); }
+	bool open_bin(const std::string& path, std::size_t n_bodies, const std::string& flavour) {
+		bin.open(path, std::ios::binary);
+		if (!bin.is_open()) return false;
+		TrajBinHeader h;
+		std::memset(&h, 0, sizeof h);
+		std::memcpy(h.magic, "NBTRJ01", 8);
+		h.n = n_bodies;
+		h.elem = (std::uint32_t)sizeof(T);
+		h.flavour = flavour == "lab5" ? 5u : 4u;
+		bin.write(reinterpret_cast<const char*>(&h), sizeof h);
+		return true;
+	}
+	void row(double time, const T* pos) {
+		if (csv) write_positions_row(*csv, time, pos, n);
+		if (bin.is_open()) {
+			bin.write(reinterpret_cast<const char*>(&time), sizeof time);
+			bin.write(reinterpret_cast<const char*>(pos), (std::streamsize)(3 * n * sizeof(T)));
+		}
+		if (!per_body.files.empty()) per_body.row(time, pos);
+	}
+	void finish() {
+		if (bin.is_open()) bin.flush();
+		per_body.flush();
+	}
+};
+
+// ---- converters of the binary sidecar (no GPU) -------------------------------------------------
+// Reads the header; returns false with `why` if the file is not a trajectory sidecar.
+inline bool read_traj_bin_header(std::ifstream& in, TrajBinHeader* h, std::string* why) {
+	in.read(reinterpret_cast<char*>(h), sizeof *h);
+	if (!in || std::memcmp(h->magic, "NBTRJ01", 8) != 0 || (h->elem != 8 && h->elem != 4) || h->n == 0 ||
+		(h->flavour != 4 && h->flavour != 5)) {
+		*why = "not a trajectory sidecar written by --traj-bin";
+		return false;
+	}
+	return true;
+}
+
+// Calls row(time, pos) for every complete record; returns the number of rows.
+template <typename T, typename F>
+long for_each_traj_row(std::ifstream& in, const TrajBinHeader& h, F&& row) {
+	std::vector<T> pos(3 * (std::size_t)h.n);
+	long rows = 0;
+	for (;;) {
+		double t;
+		in.read(reinterpret_cast<char*>(&t), sizeof t);
+		in.read(reinterpret_cast<char*>(pos.data()), (std::streamsize)(pos.size() * sizeof(T)));
+		if (!in) break;	 // a truncated last record (a killed run) is dropped
+		row(t, pos.data());
+		++rows;
+	}
+	return rows;
+}
+
+// sidecar -> the whole-system CSV a direct --traj-out run writes, byte for byte
+inline long traj_bin_to_csv(const std::string& bin_path, const std::string& csv_path, std::string* why) {
+	std::ifstream in(bin_path, std::ios::binary);
+	if (!in.is_open()) { *why = "cannot open " + bin_path; return -1; }
+	TrajBinHeader h;
+	if (!read_traj_bin_header(in, &h, why)) return -1;
+	std::ofstream out(csv_path);
+	if (!out.is_open()) { *why = "cannot open " + csv_path; return -1; }
+	out << (h.flavour == 5 ? lab5_header((std::size_t)h.n) : std::string(lab4_header()));
+	const std::size_t n = (std::size_t)h.n;
+	if (h.elem == 8)
+		return for_each_traj_row<double>(in, h, [&](double t, const double* p) { write_positions_row(out, t, p, n); });
+	return for_each_traj_row<float>(in, h, [&](double t, const float* p) { write_positions_row(out, t, p, n); });
+}
+
+// sidecar -> per-body files for bodies [first, first + count)
+inline long traj_bin_to_per_body(const std::string& bin_path, const std::string& dir, std::size_t first,
+								 std::size_t count, std::string* why) {
+	std::ifstream in(bin_path, std::ios::binary);
+	if (!in.is_open()) { *why = "cannot open " + bin_path; return -1; }
+	TrajBinHeader h;
+	if (!read_traj_bin_header(in, &h, why)) return -1;
+	PerBodyFiles files;
+	if (!files.open(dir, (std::size_t)h.n, first, count, why)) return -1;
+	long rows;
+	if (h.elem == 8) rows = for_each_traj_row<double>(in, h, [&](double t, const double* p) { files.row(t, p); });
+	else rows = for_each_traj_row<float>(in, h, [&](double t, const float* p) { files.row(t, p); });
+	files.flush();
+	return rows;
+}
+
 // ---- asynchronous trajectory sink (K4, host half) -------------------------------------------
 // The integrator thread hands (time, snapshot ticket) pairs over; this thread waits for
 // the pinned copy, formats the row and releases the ring slot, so text formatting and
@@ -273,7 +434,7 @@ struct ode_system {
 template <typename T>
 class TrajectoryWriter {
    public:
-	TrajectoryWriter(nbody_ctx* ctx, std::ostream* out, std::size_t n)
+	TrajectoryWriter(nbody_ctx* ctx, TrajectorySinks<T>* out, std::size_t n)
 		: ctx_(ctx), out_(out), n_(n), th_([this] { run(); }) {}
 	~TrajectoryWriter() { finish(); }
 	// blocks while all ring slots are in flight (back-pressure)
@@ -316,7 +477,7 @@ class TrajectoryWriter {
 			const void* p = nullptr;
 			if (nbody_snapshot_wait(ctx_, it.ticket, &p) == NBODY_OK) {
 				auto t0 = std::chrono::steady_clock::now();
-				write_positions_row(*out_, it.time, (const T*)p, n_);
+				out_->row(it.time, (const T*)p);
 				busy_ += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 			}
 			nbody_snapshot_release(ctx_, it.ticket);
@@ -328,7 +489,7 @@ class TrajectoryWriter {
 		}
 	}
 	nbody_ctx* ctx_;
-	std::ostream* out_;
+	TrajectorySinks<T>* out_;
 	std::size_t n_;
 	std::mutex mu_;
 	std::condition_variable cv_;
@@ -343,6 +504,9 @@ struct RunOptions {
 	int n_gpus = 1;
 	std::string flavour = "lab4";  // lab4: t_start row + 4-body header; lab5: N-body header, no t_start row
 	std::string traj_path;		   // "" = no trajectory (as for "4Body_random")
+	std::string traj_bin_path;	   // "" = no binary sidecar
+	std::string per_body_dir;	   // "" = no per-body traj<k>.csv files
+	std::size_t per_body_first = 0, per_body_count = 0;	 // bodies [first, first + count); 0 = to the end
 	std::string timing_path;	   // "" = derive as the reference does
 	std::string final_state_path;
 	long out_every = 1;
@@ -446,15 +610,35 @@ class Solver_N_body {
 		if (nbody_upload_aos(ctx, sys.traj_init.data())) return fail("upload");
 
 		std::ofstream traj;
-		const bool writes = rank == 0 && !opt.traj_path.empty();
-		if (writes) {
+		TrajectorySinks<T> sinks;
+		sinks.n = n;
+		if (rank == 0 && !opt.traj_path.empty()) {
 			traj.open(opt.traj_path);
 			if (!traj.is_open()) std::cout << "Could not open file for writing" << std::endl;
 			if (opt.flavour == "lab5") traj << lab5_header(n);
-			else {
-				traj << lab4_header();
-				write_bodies_coords(traj, (double)sys.t_start, sys.traj_init);	// ode_RK2_MPI.hpp:63
+			else traj << lab4_header();
+			sinks.csv = &traj;
+		}
+		auto fail_io = [&](const std::string& why) {	// as `fail`: never leave the peers waiting
+			error = why;
+			if (world > 1) {
+				std::cerr << "rank " << rank << ": " << error << std::endl;
+				std::_Exit(3);
 			}
+			nbody_destroy(ctx);
+		};
+		if (rank == 0 && !opt.traj_bin_path.empty() && !sinks.open_bin(opt.traj_bin_path, n, opt.flavour))
+			return fail_io("cannot open " + opt.traj_bin_path);
+		std::string why;
+		if (rank == 0 && !opt.per_body_dir.empty() &&
+			!sinks.per_body.open(opt.per_body_dir, n, opt.per_body_first, opt.per_body_count, &why))
+			return fail_io(why);
+		const bool writes = rank == 0 && sinks.any();
+		if (writes && opt.flavour != "lab5") {	// the t_start row (ode_RK2_MPI.hpp:63)
+			std::vector<T> pos0(3 * n);
+			for (std::size_t i = 0; i < n; ++i)
+				for (int k = 0; k < 3; ++k) pos0[3 * i + k] = sys.traj_init[i].r[k];
+			sinks.row((double)sys.t_start, pos0.data());
 		}
 		if (opt.report && nbody_energy(ctx, &result_slot(rank).e_kin0, &result_slot(rank).e_pot0))
 			return fail("energy");
@@ -462,7 +646,7 @@ class Solver_N_body {
 		RunResult& res = result_slot(rank);
 		{
 			std::unique_ptr<TrajectoryWriter<T>> writer;
-			if (writes) writer.reset(new TrajectoryWriter<T>(ctx, &traj, n));
+			if (writes) writer.reset(new TrajectoryWriter<T>(ctx, &sinks, n));
 			const auto w0 = std::chrono::steady_clock::now();
 			// The reference's loop, in T: ode_RK2_MPI.hpp:65,72,98-99
 			T t = sys.t_start + sys.tau;
@@ -517,6 +701,7 @@ class Solver_N_body {
 			res.loop_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
 			if (writer) {
 				writer->finish();
+				sinks.finish();
 				res.writer_busy_s = writer->busy_seconds();
 			}
 			res.wall_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();

@@ -8,6 +8,8 @@
 //   --tau --t-start --t-final --eps --G
 //   --precision 64|32   --scheme rk2|rk4   --gpus P   --flavour lab4|lab5
 //   --traj-out PATH  --timing-out PATH  --final-state PATH  --out-every K  --max-steps K
+//   --traj-bin PATH (binary sidecar)  --per-body-dir DIR [--per-body-first K --per-body-count M]
+//   --bin2csv BIN --bin2csv-out CSV   --bin2perbody BIN --per-body-dir DIR   (converters, no GPU)
 //   --output-folder DIR (where the reference-named CSVs go)  --report (energy, rates)
 // All computation happens behind the C ABI (include/nbody_b200.h); no CPU fallback.
 #include <cmath>
@@ -46,10 +48,13 @@ void usage() {
 		"           [--adaptive-rtol R [--adaptive-atol A]]   (step-size control, embedded pairs; --tau = first step)\n"
 		"           [--gpus 1] [--flavour lab4|lab5] [--traj-out FILE]\n"
 		"           [--timing-out FILE] [--final-state FILE] [--out-every 1] [--max-steps 0]\n"
+		"           [--traj-bin FILE] [--per-body-dir DIR [--per-body-first 1] [--per-body-count 0]]\n"
 		"           [--output-folder ../output] [--variant -1] [--pair-symmetry [0|1]] [--deterministic] [--report]\n"
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
 		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
 		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)\n"
+		"nbody_b200 --bin2csv BIN --bin2csv-out CSV   (binary trajectory -> the reference's CSV; no GPU)\n"
+		"nbody_b200 --bin2perbody BIN --per-body-dir DIR [--per-body-first 1] [--per-body-count 0]   (-> traj<k>.csv; no GPU)\n"
 		"nbody_b200 --list-tableaux   (the schemes --scheme accepts, with their coefficients; no GPU)");
 }
 
@@ -90,6 +95,14 @@ int run(const Args& a) {
 	opt.n_gpus = (int)a.num("gpus", 1);
 	opt.flavour = a.str("flavour", "lab4");
 	opt.traj_path = a.str("traj-out", "");
+	opt.traj_bin_path = a.str("traj-bin", "");
+	opt.per_body_dir = a.str("per-body-dir", "");
+	{  // bodies are numbered from 1 on the command line, as the reference's traj1..traj4 are
+		const long f = (long)a.num("per-body-first", 1);
+		opt.per_body_first = f > 1 ? (std::size_t)(f - 1) : 0;
+		const long c = (long)a.num("per-body-count", 0);
+		opt.per_body_count = c > 0 ? (std::size_t)c : 0;
+	}
 	opt.timing_path = a.str("timing-out", "");
 	opt.final_state_path = a.str("final-state", "");
 	opt.out_every = (long)a.num("out-every", 1);
@@ -198,6 +211,23 @@ int main(int argc, char** argv) {
 		} catch (int code) {
 			return code;
 		}
+		return 0;
+	}
+	if (a.has("bin2csv") || a.has("bin2perbody")) {	 // converters of the --traj-bin sidecar (no GPU)
+		std::string why;
+		long rows;
+		if (a.has("bin2csv"))
+			rows = traj_bin_to_csv(a.str("bin2csv", ""), a.str("bin2csv-out", "/dev/stdout"), &why);
+		else {
+			const long f = (long)a.num("per-body-first", 1), c = (long)a.num("per-body-count", 0);
+			rows = traj_bin_to_per_body(a.str("bin2perbody", ""), a.str("per-body-dir", "."),
+										f > 1 ? (std::size_t)(f - 1) : 0, c > 0 ? (std::size_t)c : 0, &why);
+		}
+		if (rows < 0) {
+			std::cerr << why << std::endl;
+			return 1;
+		}
+		std::cerr << rows << " rows converted" << std::endl;
 		return 0;
 	}
 	if (a.has("lab5-sweep")) {	// lab_5's test_random_bodies() (N_body.cu:438-491): RK2, T=[0,2], tau=0.1

@@ -73,6 +73,54 @@ def lab5_header(n: int) -> str:
     return "time;" + ";".join(cols) + "\n"
 
 
+# ---- the binary trajectory sidecar of `nbody_b200 --traj-bin` (host/nbody_host.hpp: TrajBinHeader)
+TRAJ_BIN_MAGIC = b"NBTRJ01\0"
+
+
+def read_traj_bin(path: str):
+    """Returns (times[rows], positions[rows, n, 3], flavour) of a sidecar file; a truncated last
+    record is dropped, as the C++ converter does."""
+    with open(path, "rb") as f:
+        head = f.read(32)
+        if len(head) != 32 or head[:8] != TRAJ_BIN_MAGIC:
+            raise ValueError("not a trajectory sidecar written by --traj-bin")
+        n = int(np.frombuffer(head, dtype="<u8", count=1, offset=8)[0])
+        elem, flavour = (int(x) for x in np.frombuffer(head, dtype="<u4", count=2, offset=16))
+        if elem not in (4, 8) or flavour not in (4, 5) or n == 0:
+            raise ValueError("not a trajectory sidecar written by --traj-bin")
+        body = f.read()
+    rec = 8 + 3 * n * elem
+    rows = len(body) // rec
+    dt = np.dtype([("t", "<f8"), ("r", "<f8" if elem == 8 else "<f4", (n, 3))])
+    a = np.frombuffer(body, dtype=dt, count=rows)
+    return a["t"].copy(), a["r"].copy(), "lab5" if flavour == 5 else "lab4"
+
+
+def traj_bin_to_csv(bin_path: str, csv_path: str) -> int:
+    """The whole-system CSV a direct run writes (same header, same rows)."""
+    t, r, flavour = read_traj_bin(bin_path)
+    with open(csv_path, "w") as f:
+        f.write(lab5_header(r.shape[1]) if flavour == "lab5" else LAB4_HEADER)
+        for k in range(t.size):
+            f.write(format_row(t[k], r[k]))
+    return int(t.size)
+
+
+def format_per_body_row(time: float, xyz) -> str:
+    """One row of a per-body file ``traj<k>.csv``: ``t;x;y;z`` (header ``time;r1;r2;r3``, the
+    layout of the reference's fixtures N_body_config/traj1.csv:1)."""
+    return "%.16e;%.16e;%.16e;%.16e\n" % (float(time), float(xyz[0]), float(xyz[1]), float(xyz[2]))
+
+
+def read_per_body(path: str) -> np.ndarray:
+    """rows x (t, x, y, z) of a per-body file -- ours or the reference's fixtures (which write
+    ``0.`` and ``1.`` for whole numbers)."""
+    with open(path) as f:
+        lines = f.read().split()
+    assert lines[0] == "time;r1;r2;r3"
+    return np.array([[float(x) for x in ln.split(";")] for ln in lines[1:]])
+
+
 def step_count(t_start, t_final, tau, dtype=np.float64) -> int:
     """Steps the reference's loop executes, t accumulated in T."""
     T = np.dtype(dtype).type

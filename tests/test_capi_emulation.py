@@ -460,6 +460,84 @@ def test_emulated_cxx_driver_reference_run_and_schemes(emulated_driver, golden, 
     assert np.abs(rows_ad[-1, 1:4] - exact).max() < 2e-5
 
 
+def test_emulated_cxx_driver_per_body_files_and_binary_sidecar(emulated_driver, golden, tmp_path):
+    """per-body traj<k>.csv files in the layout of the reference's fixtures
+    (N_body_config/traj1.csv:1) and the binary sidecar with its converters.  The lab's 4-body run
+    with RK4: each body's file against the reference's accurate solution traj<k>.csv; sidecar ->
+    CSV / per-body files byte-identical to what the direct run wrote; a 600-body run on two rank
+    threads with a body range; more than 256 files at once is refused."""
+    inp = str(tmp_path / "4body.txt")
+    _write_input(inp, golden["body4"])
+    env = dict(os.environ)
+    d = tmp_path / "pb"
+    d.mkdir()
+    csv, binf = str(tmp_path / "traj.csv"), str(tmp_path / "traj.bin")
+    r = subprocess.run([emulated_driver, "--system", "default_test", "--input", inp, "--tau", "0.1", "--t-final",
+                        "20", "--max-steps", "25", "--scheme", "rk4", "--traj-out", csv, "--traj-bin", binf,
+                        "--per-body-dir", str(d), "--timing-out", str(tmp_path / "t.csv")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    whole = np.array([[float(x) for x in ln.split(";")[:-1]] for ln in open(csv).read().splitlines()[1:]])
+    assert whole.shape == (26, 13)                               # t_start row + 25 steps
+    for k in range(4):
+        rows = lab.read_per_body(str(d / f"traj{k + 1}.csv"))
+        assert rows.shape == (26, 4)
+        assert np.array_equal(rows[:, 0], whole[:, 0]) and np.array_equal(rows[:, 1:], whole[:, 1 + 3 * k:4 + 3 * k])
+        fix = golden[f"traj{k + 1}"]                             # the reference's own per-body fixture
+        assert np.allclose(rows[:, 0], fix[:26, 0], atol=1e-12)
+        assert np.abs(rows[:, 1:] - fix[:26, 1:4]).max() < 2e-5  # RK4, tau = 0.1 (BASELINE.md: 1.2e-5 at t = 20)
+    # the sidecar holds the same numbers; both converters reproduce the direct files byte for byte
+    t, pos, flavour = lab.read_traj_bin(binf)
+    assert flavour == "lab4" and np.array_equal(t, whole[:, 0]) and np.array_equal(pos.reshape(26, 12), whole[:, 1:])
+    csv2 = str(tmp_path / "from_bin.csv")
+    assert subprocess.run([emulated_driver, "--bin2csv", binf, "--bin2csv-out", csv2]).returncode == 0
+    assert open(csv2, "rb").read() == open(csv, "rb").read()
+    assert lab.traj_bin_to_csv(binf, str(tmp_path / "py.csv")) == 26
+    assert open(tmp_path / "py.csv", "rb").read() == open(csv, "rb").read()
+    d2 = tmp_path / "pb2"
+    d2.mkdir()
+    assert subprocess.run([emulated_driver, "--bin2perbody", binf, "--per-body-dir", str(d2), "--per-body-first", "2",
+                           "--per-body-count", "2"]).returncode == 0
+    assert sorted(os.listdir(d2)) == ["traj2.csv", "traj3.csv"]
+    for nm in ("traj2.csv", "traj3.csv"):
+        assert open(d2 / nm, "rb").read() == open(d / nm, "rb").read()
+    assert open(d / "traj1.csv").readline() == "time;r1;r2;r3\n"
+    assert open(d / "traj1.csv").readlines()[1] == lab.format_per_body_row(0.0, golden["body4"][0, 1:4])
+    # a truncated sidecar (a killed run) loses only its last record
+    cut = str(tmp_path / "cut.bin")
+    open(cut, "wb").write(open(binf, "rb").read()[:-5])
+    assert lab.read_traj_bin(cut)[0].size == 25
+    assert subprocess.run([emulated_driver, "--bin2csv", cut, "--bin2csv-out", csv2]).returncode == 0
+    assert len(open(csv2).read().splitlines()) == 1 + 25
+    assert subprocess.run([emulated_driver, "--bin2csv", inp, "--bin2csv-out", csv2], capture_output=True).returncode == 1
+
+    # lab_5 flavour, FP32, 600 bodies on two rank threads, a range of bodies
+    b = generators.uniform_bodies(600, seed=45)
+    inp2 = str(tmp_path / "in600.txt")
+    _write_input(inp2, b)
+    d3 = tmp_path / "pb3"
+    d3.mkdir()
+    common = [emulated_driver, "--input", inp2, "--tau", "0.1", "--t-final", "0.15", "--precision", "32",
+              "--flavour", "lab5", "--gpus", "2", "--timing-out", str(tmp_path / "t.csv")]
+    r = subprocess.run(common + ["--per-body-dir", str(d3)], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode != 0 and "at most 256" in r.stdout + r.stderr   # 600 files at once: refused
+    csv5, bin5 = str(tmp_path / "t5.csv"), str(tmp_path / "t5.bin")
+    r = subprocess.run(common + ["--traj-out", csv5, "--traj-bin", bin5, "--per-body-dir", str(d3),
+                                 "--per-body-first", "599", "--per-body-count", "0"],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert sorted(os.listdir(d3)) == ["traj599.csv", "traj600.csv"]
+    lines = open(csv5).read().splitlines()
+    assert lines[0] + "\n" == lab.lab5_header(600) and len(lines) == 1 + 2       # no t_start row in lab_5
+    last = np.array([float(x) for x in lines[-1].split(";")[:-1]])
+    rows = lab.read_per_body(str(d3 / "traj600.csv"))
+    assert np.array_equal(rows[-1], np.concatenate([last[:1], last[-3:]]))
+    t5, pos5, fl5 = lab.read_traj_bin(bin5)
+    assert fl5 == "lab5" and pos5.dtype == np.float32 and pos5.shape == (2, 600, 3)
+    assert subprocess.run([emulated_driver, "--bin2csv", bin5, "--bin2csv-out", csv2]).returncode == 0
+    assert open(csv2, "rb").read() == open(csv5, "rb").read()
+
+
 def test_emulated_cxx_driver_deterministic_flag_writes_identical_files(emulated_driver, tmp_path):
     """`nbody_b200 --deterministic`: the final-state file and the trajectory are byte-identical for
     different unit orders (EMU_CTA_SHUFFLE), one rank thread and two."""

@@ -92,3 +92,47 @@ def test_lab5_sweep_mode(tmp_path):
     t = open(out / "res_10k_float_128_.csv").read().splitlines()
     assert t[0] == "type;n_bodies;n_steps;block_size;time_taken;avg_exec_time"
     assert t[1].startswith("float;10000;20;")   # (2-0)/0.1 in float = 20
+
+
+def test_per_body_files_and_binary_sidecar(golden, tmp_path):
+    """The lab's 4-body run to t = 20 with RK4: every body's traj<k>.csv against the reference's own
+    per-body fixture N_body_config/traj<k>.csv (max error 1.2157e-5 over 4 bodies x 200
+    samples); the binary sidecar converts to the direct CSV and per-body files byte for byte; a
+    20k-body run writes a range of bodies and a sidecar of 3 n sizeof(T) bytes per row."""
+    d = tmp_path / "pb"
+    d.mkdir()
+    csv, binf = tmp_path / "traj.csv", tmp_path / "traj.bin"
+    run("--system", "default_test", "--input", IN4, "--tau", 0.1, "--scheme", "rk4", "--traj-out", csv,
+        "--traj-bin", binf, "--per-body-dir", d, "--timing-out", tmp_path / "t.csv")
+    _, whole = parse(csv)
+    assert whole.shape == (201, 13)
+    worst = 0.0
+    for k in range(4):
+        rows = lab.read_per_body(str(d / f"traj{k + 1}.csv"))
+        fix = golden[f"traj{k + 1}"]
+        assert rows.shape == (201, 4) and np.array_equal(rows[:, 1:], whole[:, 1 + 3 * k:4 + 3 * k])
+        worst = max(worst, float(np.abs(rows[:, 1:] - fix[:201, 1:4]).max()))
+    assert abs(worst - 1.2157e-5) < 2e-8                           # the reference's known answer for RK4
+    run("--bin2csv", binf, "--bin2csv-out", tmp_path / "again.csv")
+    assert open(tmp_path / "again.csv", "rb").read() == open(csv, "rb").read()
+    d2 = tmp_path / "pb2"
+    d2.mkdir()
+    run("--bin2perbody", binf, "--per-body-dir", d2)
+    for k in range(1, 5):
+        assert open(d2 / f"traj{k}.csv", "rb").read() == open(d / f"traj{k}.csv", "rb").read()
+    t, pos, flavour = lab.read_traj_bin(str(binf))
+    assert flavour == "lab4" and np.array_equal(pos.reshape(201, 12), whole[:, 1:])
+
+    n = 20000
+    inp = tmp_path / "in.txt"
+    run("--generate", "uniform", "--n", n, "--generate-out", inp)
+    d3 = tmp_path / "pb3"
+    d3.mkdir()
+    run("--input", inp, "--scheme", "rk4", "--tau", 0.1, "--t-final", 0.35, "--flavour", "lab5", "--traj-bin",
+        tmp_path / "big.bin", "--per-body-dir", d3, "--per-body-first", 19999, "--timing-out", tmp_path / "t.csv")
+    assert sorted(os.listdir(d3)) == ["traj19999.csv", "traj20000.csv"]
+    t, pos, flavour = lab.read_traj_bin(str(tmp_path / "big.bin"))
+    assert flavour == "lab5" and pos.shape == (4, n, 3)
+    assert os.path.getsize(tmp_path / "big.bin") == 32 + 4 * (8 + 3 * n * 8)
+    rows = lab.read_per_body(str(d3 / "traj20000.csv"))
+    assert np.array_equal(rows[:, 1:], pos[:, n - 1, :]) and np.array_equal(rows[:, 0], t)
