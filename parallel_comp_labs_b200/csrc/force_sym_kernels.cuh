@@ -1,5 +1,5 @@
-// force_sym_kernels.cuh -- K1s: the pair-symmetric variant of the all-pairs acceleration (opt-in,
-// nbody_set_option("pair_symmetry", 1), one GPU).
+// force_sym_kernels.cuh -- K1s: the pair-symmetric kernel of the all-pairs acceleration (the default
+// for n >= 2048, option "pair_symmetry"; on several GPUs the ranks split the blocks of one schedule).
 //
 // Same operator as force_kernels.cuh (reference: lab_4 .../struct_ode_system.hpp:60-75,
 // lab_5 N_body.cu:134-195), same per-pair arithmetic, but every pair of DISTINCT bodies is
@@ -20,7 +20,7 @@
 //    collected the reaction of all 32*I i-bodies and is back in its home lane.  It is then added
 //    to the j-side sum array with one RED per component (fire-and-forget atomics: the summation
 //    ORDER of the j-side contributions depends on scheduling, so results are reproducible only
-//    to rounding, unlike the default kernel);
+//    to rounding, unlike the one-sided kernel -- or, ACC = 2, as exact fixed-point integers);
 //  * the block's own tiles are met one-sidedly with the exact clamp (this is where the self
 //    pairs are), exactly as K1 does;
 //  * clamp: as in K1 the hot loop is unclamped and tracks the smallest key(r^2); a strip that may

@@ -1,9 +1,7 @@
-"""Parity of the opt-in pair-symmetric force kernel (option "pair_symmetry", one GPU:
-parallel_comp_labs_b200/csrc/force_sym_kernels.cuh) against the oracle and against the default
-kernel.  Same tolerances as tests/test_gpu_parity.py.  The file name sorts last on purpose: this
-mode was written after the round's GPU budget was spent (its decomposition is proven on the CPU by
-tests/test_host_logic.py::test_pair_symmetric_schedule_covers_every_pair_once), so a failure here
-must not mask the default path's suite under `pytest -x`."""
+"""Parity of the pair-symmetric force kernel (option "pair_symmetry"; the default for n >= 2048:
+parallel_comp_labs_b200/csrc/force_sym_kernels.cuh) against the oracle and against the one-sided
+kernel.  Same tolerances as tests/test_gpu_parity.py.  Its decomposition is also proven on the CPU
+by tests/test_host_logic.py::test_pair_symmetric_schedule_covers_every_pair_once."""
 import numpy as np
 import pytest
 
