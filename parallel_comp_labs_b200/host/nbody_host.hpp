@@ -340,8 +340,9 @@ struct TrajectorySinks {
 	std::ostream* csv = nullptr;   // whole-system CSV (header already written by the caller)
 	std::ofstream bin;			   // binary sidecar
 	PerBodyFiles per_body;
+	std::vector<std::vector<double>>* keep = nullptr;  // rows {t, 3n positions} kept in memory
 	std::size_t n = 0;
-	bool any() const { return csv || bin.is_open() || !per_body.files.empty(); }
+	bool any() const { return csv || keep || bin.is_open() || !per_body.files.empty(); }
 	bool open_bin(const std::string& path, std::size_t n_bodies, const std::string& flavour) {
 		bin.open(path, std::ios::binary);
 		if (!bin.is_open()) return false;
@@ -361,6 +362,12 @@ struct TrajectorySinks {
 			bin.write(reinterpret_cast<const char*>(pos), (std::streamsize)(3 * n * sizeof(T)));
 		}
 		if (!per_body.files.empty()) per_body.row(time, pos);
+		if (keep) {
+			std::vector<double> r(1 + 3 * n);
+			r[0] = time;
+			for (std::size_t i = 0; i < 3 * n; ++i) r[1 + i] = (double)pos[i];
+			keep->push_back(std::move(r));
+		}
 	}
 	void finish() {
 		if (bin.is_open()) bin.flush();
@@ -424,6 +431,32 @@ inline long traj_bin_to_per_body(const std::string& bin_path, const std::string&
 	if (h.elem == 8) rows = for_each_traj_row<double>(in, h, [&](double t, const double* p) { files.row(t, p); });
 	else rows = for_each_traj_row<float>(in, h, [&](double t, const float* p) { files.row(t, p); });
 	files.flush();
+	return rows;
+}
+
+// A per-body file "time;r1;r2;r3" + "t;x;y;z" rows -- ours or the reference's fixtures
+// (N_body_config/traj1.csv, which write "0." and "1." for whole numbers): rows of {t, x, y, z}.
+inline std::vector<std::array<double, 4>> read_per_body_file(const std::string& path) {
+	std::ifstream in(path);
+	if (!in.is_open()) {
+		std::cout << "file is't open" << std::endl;	 // as read_data does (read_write_utils.hpp:15-19)
+		throw 1;
+	}
+	std::vector<std::array<double, 4>> rows;
+	std::string line;
+	std::getline(in, line);	 // header
+	while (std::getline(in, line)) {
+		std::array<double, 4> r{};
+		const char* p = line.c_str();
+		int k = 0;
+		for (; k < 4; ++k) {
+			char* end = nullptr;
+			r[k] = std::strtod(p, &end);
+			if (end == p) break;
+			p = *end == ';' ? end + 1 : end;
+		}
+		if (k == 4) rows.push_back(r);
+	}
 	return rows;
 }
 
@@ -507,6 +540,7 @@ struct RunOptions {
 	std::string traj_bin_path;	   // "" = no binary sidecar
 	std::string per_body_dir;	   // "" = no per-body traj<k>.csv files
 	std::size_t per_body_first = 0, per_body_count = 0;	 // bodies [first, first + count); 0 = to the end
+	bool keep_rows = false;		   // keep every trajectory row in Solver_N_body::kept_rows
 	std::string timing_path;	   // "" = derive as the reference does
 	std::string final_state_path;
 	long out_every = 1;
@@ -539,6 +573,7 @@ class Solver_N_body {
 	std::string output_folder = "../output/";
 	std::vector<Body<T>> final_state;
 	RunResult result;
+	std::vector<std::vector<double>> kept_rows;	 // RunOptions::keep_rows: {t, x1, y1, z1, ...} per row
 
 	Solver_N_body() = default;
 	Solver_N_body(T tol_, std::string output_folder_, std::string file_name_)
@@ -633,6 +668,10 @@ class Solver_N_body {
 		if (rank == 0 && !opt.per_body_dir.empty() &&
 			!sinks.per_body.open(opt.per_body_dir, n, opt.per_body_first, opt.per_body_count, &why))
 			return fail_io(why);
+		if (rank == 0 && opt.keep_rows) {
+			kept_rows.clear();
+			sinks.keep = &kept_rows;
+		}
 		const bool writes = rank == 0 && sinks.any();
 		if (writes && opt.flavour != "lab5") {	// the t_start row (ode_RK2_MPI.hpp:63)
 			std::vector<T> pos0(3 * n);

@@ -12,6 +12,7 @@
 //   --bin2csv BIN --bin2csv-out CSV   --bin2perbody BIN --per-body-dir DIR   (converters, no GPU)
 //   --output-folder DIR (where the reference-named CSVs go)  --report (energy, rates)
 // All computation happens behind the C ABI (include/nbody_b200.h); no CPU fallback.
+#include <array>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -53,9 +54,97 @@ void usage() {
 		"nbody_b200 --generate uniform|plummer --n N [--seed S] --generate-out FILE   (input generator)\n"
 		"nbody_b200 --lab5-sweep DIR [--precision 32] [--output-folder ../output]   (lab_5 test_random_bodies)\n"
 		"nbody_b200 --reformat IN --reformat-out OUT   (parse a body file, rewrite it losslessly; no GPU)\n"
+		"nbody_b200 --convergence FIXTURE_DIR --input 4body.txt [--scheme rk2] [--taus 0.1,0.05,0.025]\n"
+		"           (the reference's commented convergence runs, N_body.cpp:69-79: error of each run against\n"
+		"            FIXTURE_DIR/traj<k>.csv and the observed order)\n"
 		"nbody_b200 --bin2csv BIN --bin2csv-out CSV   (binary trajectory -> the reference's CSV; no GPU)\n"
 		"nbody_b200 --bin2perbody BIN --per-body-dir DIR [--per-body-first 1] [--per-body-count 0]   (-> traj<k>.csv; no GPU)\n"
 		"nbody_b200 --list-tableaux   (the schemes --scheme accepts, with their coefficients; no GPU)");
+}
+
+// The reference's commented convergence runs (lab_4 N_body.cpp:69-79: ode_system_default_test at
+// tau = 0.1, 0.05, 0.025) as one command: each run's rows at t = 0.1 k against the reference's
+// accurate per-body solution FIXTURE_DIR/traj<k>.csv, max |error| over bodies, samples and
+// coordinates, and the observed order log2(err(tau) / err(tau/2)).  One JSON line on stdout.
+template <typename T>
+int run_convergence(const Args& a) {
+	const std::string dir = a.str("convergence", ".");
+	std::vector<double> taus;
+	{
+		std::string list = a.str("taus", "0.1,0.05,0.025");
+		std::size_t pos = 0;
+		while (pos < list.size()) {
+			std::size_t end = list.find(',', pos);
+			if (end == std::string::npos) end = list.size();
+			taus.push_back(std::strtod(list.substr(pos, end - pos).c_str(), nullptr));
+			pos = end + 1;
+		}
+	}
+	RunOptions opt;
+	const std::string scheme = a.str("scheme", "rk2");
+	opt.scheme = scheme == "rk4" ? NBODY_RK4 : NBODY_RK2;
+	if (scheme != "rk2" && scheme != "rk4") {
+		if (!find_tableau(scheme)) {
+			std::cerr << "unknown --scheme " << scheme << std::endl;
+			return 2;
+		}
+		opt.tableau = scheme;
+	}
+	opt.n_gpus = (int)a.num("gpus", 1);
+	opt.keep_rows = true;
+	opt.timing_path = a.str("timing-out", "/dev/null");
+	opt.pair_symmetry = a.has("pair-symmetry") ? (a.str("pair-symmetry", "1") == "0" ? 0 : 1) : -1;
+	std::vector<std::vector<std::array<double, 4>>> truth;
+	std::vector<double> errs;
+	try {
+		for (const double tau : taus) {
+			ode_system<T> sys;
+			sys.ode_system_default_test((T)tau, (T)a.num("eps", 1e-6), (T)a.num("G", 6.67e-11),
+										a.str("input", "./include/N_body/N_body_config/4body.txt"));
+			sys.n_time_steps = (int)((sys.t_final - sys.t_start) / sys.tau);
+			sys.N_bodies = (int)sys.traj_init.size();
+			if (truth.empty())
+				for (std::size_t k = 1; k <= sys.traj_init.size(); ++k)
+					truth.push_back(read_per_body_file(dir + "/traj" + std::to_string(k) + ".csv"));
+			Solver_N_body<T> solver;
+			solver.output_folder = a.str("output-folder", "../output");
+			solver.solve_parallel_CUDA(sys, opt);
+			// rows: t_start, then one per step; the fixtures sample t = 0, 0.1, 0.2, ...
+			const double dt_fix = truth[0].size() > 1 ? truth[0][1][0] - truth[0][0][0] : 0.1;
+			const long stride = std::lround(dt_fix / tau);
+			if (stride < 1 || std::fabs((double)stride * tau - dt_fix) > 1e-9 * dt_fix) {
+				std::cerr << "--taus: " << tau << " does not divide the fixtures' sampling interval " << dt_fix
+						  << std::endl;
+				return 2;
+			}
+			double err = 0;
+			for (std::size_t k = 0; k < truth.size(); ++k)
+				for (std::size_t s = 0; s < truth[k].size(); ++s) {
+					const std::size_t row = s * (std::size_t)stride;
+					if (row >= solver.kept_rows.size()) break;
+					for (int c = 0; c < 3; ++c)
+						err = std::max(err, std::fabs(solver.kept_rows[row][1 + 3 * k + c] - truth[k][s][1 + c]));
+				}
+			errs.push_back(err);
+		}
+	} catch (int code) {
+		return code;
+	} catch (const char* msg) {
+		std::cerr << msg << std::endl;
+		return 2;
+	} catch (const std::exception& e) {
+		std::cerr << "error: " << e.what() << std::endl;
+		return 3;
+	}
+	std::printf("{\"scheme\": \"%s\", \"taus\": [", scheme.c_str());
+	for (std::size_t i = 0; i < taus.size(); ++i) std::printf("%s%.17g", i ? ", " : "", taus[i]);
+	std::printf("], \"max_abs_err\": [");
+	for (std::size_t i = 0; i < errs.size(); ++i) std::printf("%s%.10e", i ? ", " : "", errs[i]);
+	std::printf("], \"observed_order\": [");
+	for (std::size_t i = 0; i + 1 < errs.size(); ++i)
+		std::printf("%s%.4f", i ? ", " : "", std::log(errs[i] / errs[i + 1]) / std::log(taus[i] / taus[i + 1]));
+	std::printf("]}\n");
+	return 0;
 }
 
 template <typename T>
@@ -253,6 +342,7 @@ int main(int argc, char** argv) {
 		return ran ? 0 : 1;
 	}
 	const int prec = (int)a.num("precision", 64);
+	if (a.has("convergence")) return prec == 32 ? run_convergence<float>(a) : run_convergence<double>(a);
 	if (prec == 64) return run<double>(a);
 	if (prec == 32) return run<float>(a);
 	std::cerr << "--precision must be 64 or 32" << std::endl;

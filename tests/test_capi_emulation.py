@@ -538,6 +538,31 @@ def test_emulated_cxx_driver_per_body_files_and_binary_sidecar(emulated_driver, 
     assert open(csv2, "rb").read() == open(csv5, "rb").read()
 
 
+def test_emulated_cxx_driver_convergence_study(emulated_driver, golden, tmp_path):
+    """`nbody_b200 --convergence DIR`: the reference's commented convergence runs (N_body.cpp:69-79,
+    tau = 0.1 / 0.05 / 0.025 of the 4-body test) as one command, errors against the reference's own
+    per-body fixtures traj{1..4}.csv: the known answers 4.0853e-2 / 1.0966e-2 / 2.8310e-3, order 2."""
+    import json
+    inp = str(tmp_path / "4body.txt")
+    _write_input(inp, golden["body4"])
+    for k in range(1, 5):                         # the fixtures in their own layout
+        with open(tmp_path / f"traj{k}.csv", "w") as f:
+            f.write("time;r1;r2;r3\n")
+            for row in golden[f"traj{k}"]:
+                f.write(";".join(repr(float(x)) for x in row) + "\n")
+    r = subprocess.run([emulated_driver, "--convergence", str(tmp_path), "--input", inp, "--output-folder",
+                        str(tmp_path)], capture_output=True, text=True, timeout=900, env=dict(os.environ))
+    assert r.returncode == 0, r.stdout + r.stderr
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["scheme"] == "rk2" and res["taus"] == [0.1, 0.05, 0.025]
+    for got, want in zip(res["max_abs_err"], (4.0853e-2, 1.0966e-2, 2.8310e-3)):
+        assert abs(got - want) < 5e-6
+    assert all(abs(o - 2.0) < 0.15 for o in res["observed_order"])
+    r = subprocess.run([emulated_driver, "--convergence", str(tmp_path), "--input", inp, "--taus", "0.03",
+                        "--output-folder", str(tmp_path)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 2 and "does not divide" in r.stderr
+
+
 def test_emulated_cxx_driver_deterministic_flag_writes_identical_files(emulated_driver, tmp_path):
     """`nbody_b200 --deterministic`: the final-state file and the trajectory are byte-identical for
     different unit orders (EMU_CTA_SHUFFLE), one rank thread and two."""

@@ -136,3 +136,24 @@ def test_per_body_files_and_binary_sidecar(golden, tmp_path):
     assert os.path.getsize(tmp_path / "big.bin") == 32 + 4 * (8 + 3 * n * 8)
     rows = lab.read_per_body(str(d3 / "traj20000.csv"))
     assert np.array_equal(rows[:, 1:], pos[:, n - 1, :]) and np.array_equal(rows[:, 0], t)
+
+
+def test_convergence_study_reproduces_the_known_answers(golden, tmp_path):
+    """`nbody_b200 --convergence DIR` = the reference's commented convergence runs (N_body.cpp:69-79)
+    as one command: RK2 at tau = 0.1 / 0.05 / 0.025 against traj{1..4}.csv gives 4.0853e-2 /
+    1.0966e-2 / 2.8310e-3 (order 2), RK4 at 0.1 gives 1.2157e-5."""
+    for k in range(1, 5):
+        with open(tmp_path / f"traj{k}.csv", "w") as f:
+            f.write("time;r1;r2;r3\n")
+            for row in golden[f"traj{k}"]:
+                f.write(";".join(repr(float(x)) for x in row) + "\n")
+    out = run("--convergence", tmp_path, "--input", IN4, "--output-folder", tmp_path)
+    res = json.loads(out.strip().splitlines()[-1])
+    assert res["taus"] == [0.1, 0.05, 0.025]
+    for got, want in zip(res["max_abs_err"], (4.0853e-2, 1.0966e-2, 2.8310e-3)):
+        assert abs(got - want) < 5e-6
+    assert all(abs(o - 2.0) < 0.15 for o in res["observed_order"])
+    out = run("--convergence", tmp_path, "--input", IN4, "--scheme", "rk4", "--taus", "0.1",
+              "--output-folder", tmp_path)
+    res = json.loads(out.strip().splitlines()[-1])
+    assert abs(res["max_abs_err"][0] - 1.2157e-5) < 5e-8 and res["observed_order"] == []
