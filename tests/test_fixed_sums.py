@@ -100,3 +100,27 @@ def test_non_finite_and_out_of_window_poison_the_row(fx):
     assert poison == 1
     limbs, poison = accumulate(fx, np.array([2.0 ** (bits - 101)]), -100)   # just inside
     assert poison == 0 and fx.fx_value(limbs.ctypes.data, -100) == 2.0 ** (bits - 101)
+
+
+def test_property_random_lists_any_order_correct_rounding(fx):
+    """Property test (hypothesis): arbitrary finite doubles spread over the whole window -- fast path,
+    slow path and partly truncated values mixed -- sum to the same limbs in any order, and read back
+    as the correctly rounded exact (truncated) sum."""
+    from hypothesis import given, settings, strategies as st
+    bits = 32 * fx.fx_limbs()
+
+    @settings(max_examples=150, deadline=None)
+    @given(st.integers(-400, 400), st.lists(st.tuples(st.floats(0.5, 1.0, exclude_max=True), st.integers(-230, -3),
+                                                       st.booleans()), min_size=1, max_size=60), st.randoms())
+    def check(top, terms, rnd):
+        e0 = top - bits
+        x = np.array([np.ldexp(m, top + ex) * (-1.0 if neg else 1.0) for m, ex, neg in terms])
+        limbs, poison = accumulate(fx, x, e0)
+        assert poison == 0
+        perm = list(range(x.size))
+        rnd.shuffle(perm)
+        l2, _ = accumulate(fx, x[perm], e0)
+        assert np.array_equal(limbs, l2)
+        assert fx.fx_value(limbs.ctypes.data, e0) == float(exact_truncated(x, e0))
+
+    check()
