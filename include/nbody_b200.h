@@ -238,6 +238,47 @@ int nbody_energy(nbody_ctx* ctx, double* kinetic, double* potential);
  * Not in the reference.  Collective when world > 1. */
 int nbody_diagnostics(nbody_ctx* ctx, double out[9]);
 
+/* Acceleration of n bodies WITHOUT a context and WITHOUT any device allocation.
+ * No counterpart in the reference (its programs cudaMalloc whatever they need,
+ * lab_5 N_body.cu:257-288); the argument list is the one lab_5's calc_acceleration takes.
+ *
+ * Who needs it: every other compute entry point works on an nbody_ctx, and nbody_create (and a few
+ * calls after it, lazily) reserve device memory with cudaMalloc.  Some hosts cannot afford that:
+ * an application whose own pool already holds all of the GPU's memory (a cudaMalloc from this
+ * library would fail or evict nothing), a service with a fixed per-process memory budget, or a
+ * latency-sensitive loop that must not hit the device-wide synchronisation and driver lock that
+ * cudaMalloc / cudaFree imply.  Such a host already OWNS device arrays of masses and positions; it
+ * passes them in, together with the array the accelerations go to, and this call does the rest.
+ *
+ * What it computes: the operator of nbody_rhs (struct_ode_system.hpp:60-75: clamped softening,
+ * times -G) for all n rows, by the pair-symmetric force kernel in its 256-row build with general
+ * masses.  The kernel's working memory -- a padded {x,y,z,m} copy of the bodies, the row sums both
+ * sides of a pair are added to, the work-ticket counter -- lives in ONE array that is part of the
+ * library image (about NBODY_NOALLOC_SCRATCH_BYTES on every GPU the library is used on, from the
+ * moment the library's code is loaded there until the process ends).  Hence the limit:
+ * n <= NBODY_NOALLOC_MAX_BODIES, larger n is NBODY_ERR_ARG and nothing is launched.
+ *
+ *   device      CUDA device the three arrays live on (made current for the call)
+ *   precision   64: T = double, T4 = double4;   32: T = float, T4 = float4
+ *   m_dev       device, T[n]   masses
+ *   r4_dev      device, T4[n]  positions, .w ignored           (16-/32-byte aligned)
+ *   acc_dev     device, T[3n]  accelerations, 3 x T per body as nbody_rhs writes them
+ *   stream      a cudaStream_t passed as void*; NULL = the default stream
+ *
+ * The work (three kernels) is enqueued on `stream` and the call returns; the caller synchronises
+ * the stream before it reads acc_dev.  Sums are floating-point atomics as in the default kernel:
+ * equal to nbody_rhs up to rounding, not bit for bit.
+ * The first call on a device looks the array's device address up and records it (a few
+ * microseconds, no allocation); make that first call outside any stream capture.
+ * The array is shared by all calls and keeps what the last call left in it; each call clears the
+ * parts that must start at zero itself.  Two calls whose work can be on the same GPU at the same
+ * time (different streams, or different host threads with different streams) would overwrite each
+ * other's working memory: order them on one stream or with events. */
+#define NBODY_NOALLOC_MAX_BODIES 65536
+#define NBODY_NOALLOC_SCRATCH_BYTES (4u << 20)
+int nbody_rhs_noalloc(int device, int precision, size_t n, const void* m_dev, const void* r4_dev,
+					  void* acc_dev, double grav_G, double eps, void* stream);
+
 int nbody_get_timing(nbody_ctx* ctx, nbody_timing* out);
 /* Up to `cap` entries of the last call's trace (option "trace"); *n_out = entries recorded. Syncs. */
 int nbody_get_trace(nbody_ctx* ctx, nbody_trace_entry* out, size_t cap, size_t* n_out);

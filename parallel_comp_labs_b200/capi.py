@@ -115,6 +115,8 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_host_free.argtypes = [vp]
     L.nbody_host_free.restype = None
     L.nbody_measure_fma_peak.argtypes = [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+    if hasattr(L, "nbody_rhs_noalloc"):
+        L.nbody_rhs_noalloc.argtypes = [C.c_int, C.c_int, sz, vp, vp, vp, C.c_double, C.c_double, vp]
     return L
 
 
@@ -140,6 +142,24 @@ def nccl_unique_id() -> bytes:
     if rc:
         raise NBodyError(lib().nbody_last_error(None).decode())
     return buf.raw
+
+
+NOALLOC_MAX_BODIES = 65536
+
+
+def rhs_noalloc(n: int, m_dev: int, r4_dev: int, acc_dev: int, precision: int = 64, device: int = 0,
+                G: float = 6.67e-11, eps: float = 1e-6, stream: int | None = None) -> None:
+    """nbody_rhs_noalloc: accelerations of n bodies the caller already holds on the device.
+
+    For hosts that cannot let the library reserve device memory (everything else here goes through
+    a Context, whose creation calls cudaMalloc): `m_dev`, `r4_dev`, `acc_dev` are DEVICE addresses
+    (ints) of T[n] masses, T4[n] positions and T[3n] output.  The work is enqueued on `stream`
+    (a cudaStream_t as int; None = default stream) and NOT waited for.  n is limited to
+    NOALLOC_MAX_BODIES because the kernel's working memory is a fixed array inside the library;
+    calls that can run on the GPU at the same time share that array and must be ordered."""
+    rc = lib().nbody_rhs_noalloc(device, precision, n, m_dev, r4_dev, acc_dev, G, eps, stream)
+    if rc:
+        raise NBodyError(lib().nbody_last_error(None).decode())
 
 
 def measure_fma_peak(precision: int = 64, ms_target: float = 200.0, device: int = 0) -> float:

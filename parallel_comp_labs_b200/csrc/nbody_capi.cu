@@ -2083,3 +2083,192 @@ int nbody_measure_fma_peak(int device, int precision, double ms_target, double* 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ nbody_rhs_noalloc
+// The acceleration of n bodies for hosts that cannot let this library reserve device memory (an
+// application pool that already holds the whole GPU, a fixed per-process budget, a loop that must
+// not run into the device-wide synchronisation of cudaMalloc / cudaFree): see include/nbody_b200.h.
+// Nothing below calls cudaMalloc, cudaFree or any routine that allocates on the device.  The
+// working memory of the pair-symmetric kernel sits in g_noalloc_scratch, an array that is part of
+// the library image: every GPU on which this library's code gets loaded carries these 4 MiB until
+// the process ends, which is why the entry point stops at NBODY_NOALLOC_MAX_BODIES.
+//
+// In HOST code the name g_noalloc_scratch is only a handle for the runtime, not a device address
+// (passing it to a kernel would make the kernel touch host memory or fault), so the host asks the
+// runtime once per device -- with that device current -- where the array lives there
+// (cudaGetSymbolAddress) and hands the kernels that pointer.
+//
+// Layout (bytes):  [0, 256)  work-ticket counter of the force kernel
+//                  [256, 256 + MAX*32)                 V4[n_pad] padded {x,y,z,m}
+//                  [256 + MAX*32, 256 + MAX*32 + MAX*24)  T[3][n_pad] row sums
+// with MAX = NBODY_NOALLOC_MAX_BODIES and the element sizes of FP64 (FP32 uses half of each part).
+namespace nbody {
+constexpr size_t NOALLOC_POS_OFF = 256;
+constexpr size_t NOALLOC_SUM_OFF = NOALLOC_POS_OFF + (size_t)NBODY_NOALLOC_MAX_BODIES * 32;
+constexpr size_t NOALLOC_END = NOALLOC_SUM_OFF + (size_t)NBODY_NOALLOC_MAX_BODIES * 24;
+static_assert(NOALLOC_END <= NBODY_NOALLOC_SCRATCH_BYTES, "scratch layout exceeds the stated size");
+static_assert(NBODY_NOALLOC_MAX_BODIES % 256 == 0, "the limit is a whole number of j-tiles");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NBODY_NOALLOC_SCRATCH_BYTES];
+
+// Everything a call needs from the shared array in the state it must start from: the bodies in the
+// kernel's layout (pad rows: zero mass at the origin, they add exactly 0 to every sum), the row
+// sums and the ticket counter at zero -- whatever the previous call left there.
+template <typename T>
+__global__ void __launch_bounds__(256)
+	noalloc_prepare_kernel(const T* __restrict__ m, const typename V4<T>::type* __restrict__ r,
+						   unsigned char* scratch, unsigned n, unsigned n_pad) {
+	typedef typename V4<T>::type vec4;
+	vec4* pos = reinterpret_cast<vec4*>(scratch + NOALLOC_POS_OFF);
+	T* sums = reinterpret_cast<T*>(scratch + NOALLOC_SUM_OFF);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i == 0) *reinterpret_cast<unsigned*>(scratch) = 0u;
+	if (i >= n_pad) return;
+	vec4 q;
+	q.x = q.y = q.z = q.w = T(0);
+	if (i < n) {
+		const vec4 p = r[i];
+		q.x = p.x; q.y = p.y; q.z = p.z;
+		q.w = m[i];
+	}
+	pos[i] = q;
+	sums[i] = T(0);
+	sums[(size_t)n_pad + i] = T(0);
+	sums[2 * (size_t)n_pad + i] = T(0);
+}
+
+// row sums -> accelerations, the same two roundings as stage_kernel (mass scale 1, then -G)
+template <typename T>
+__global__ void __launch_bounds__(256)
+	noalloc_finish_kernel(const unsigned char* scratch, T* __restrict__ acc, unsigned n,
+						  unsigned n_pad, T minusG) {
+	const T* sums = reinterpret_cast<const T*>(scratch + NOALLOC_SUM_OFF);
+	const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+#pragma unroll
+	for (int c = 0; c < 3; ++c) {
+		const T s = add_rn(T(0), sums[(size_t)c * n_pad + i]);
+		acc[3 * (size_t)i + c] = mul_rn(mul_rn(s, T(1)), minusG);
+	}
+}
+}  // namespace nbody
+
+namespace {
+// device address of g_noalloc_scratch per device (nullptr = not looked up yet) and what the set-up
+// learnt about the device on the way
+struct NoallocDev {
+	unsigned char* scratch = nullptr;
+	int n_sm = 0, per_sm[2] = {0, 0};  // resident CTAs per SM of the FP64 / FP32 build
+};
+constexpr int NOALLOC_MAX_DEVICES = 64;
+NoallocDev g_noalloc_dev[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mu;
+
+// the 256-row builds of the pair-symmetric kernel (128 threads x 2 i-bodies), general masses
+const SymVariant& noalloc_variant(int precision) { return precision == 64 ? g_sym64[3] : g_sym32[2]; }
+
+// once per device, with that device current: where does the array live on THIS GPU?
+int noalloc_setup(int device, NoallocDev** out) {
+	nbody_ctx* ctx = nullptr;  // CK / fail report through nbody_last_error(NULL)
+	std::lock_guard<std::mutex> lock(g_noalloc_mu);
+	NoallocDev& d = g_noalloc_dev[device];
+	*out = &d;
+	if (d.scratch) return NBODY_OK;
+	cudaDeviceProp prop;
+	CK(cudaGetDeviceProperties(&prop, device));
+	if (prop.major != 10)
+		return fail(ctx, NBODY_ERR_NO_DEVICE,
+					std::string("device '") + prop.name +
+						"' is not sm_100 (Blackwell B200); the kernels are built for sm_100a only");
+	void* p = nullptr;
+	const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+	if (e != cudaSuccess || !p)
+		return fail(ctx, NBODY_ERR_CUDA,
+					std::string("nbody_rhs_noalloc: cudaGetSymbolAddress(g_noalloc_scratch): ") +
+						cudaGetErrorString(e));
+	for (int k = 0; k < 2; ++k) {
+		const SymVariant& v = noalloc_variant(k == 0 ? 64 : 32);
+		CK(cudaFuncSetAttribute(v.fn[0], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem));
+		CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.per_sm[k], v.fn[0], v.threads, v.smem));
+		if (d.per_sm[k] < 1) return fail(ctx, NBODY_ERR_CUDA, "force kernel does not fit on an SM");
+	}
+	d.n_sm = prop.multiProcessorCount;
+	d.scratch = static_cast<unsigned char*>(p);	 // last: marks the set-up as complete
+	return NBODY_OK;
+}
+
+template <typename T>
+int noalloc_enqueue(const NoallocDev& d, size_t n, const void* m_dev, const void* r4_dev,
+					void* acc_dev, double G, double eps, cudaStream_t st) {
+	nbody_ctx* ctx = nullptr;
+	typedef typename V4<T>::type vec4;
+	const int prec = sizeof(T) == 8 ? 64 : 32;
+	const SymVariant& v = noalloc_variant(prec);
+	const unsigned TJ = 256, block = (unsigned)(v.threads * v.ipt);	 // == TJ: one tile per block
+	const unsigned n_pad = (unsigned)((n + TJ - 1) / TJ * TJ);
+	const unsigned nb = n_pad / block;
+	NB_LAUNCH(noalloc_prepare_kernel<T>, dim3(n_pad / 256), dim3(256), 0, st,
+			  (const T*)m_dev, (const vec4*)r4_dev, d.scratch, (unsigned)n, n_pad);
+	CK(cudaGetLastError());
+
+	SymParams p;
+	p.pos = d.scratch + NOALLOC_POS_OFF;
+	p.aj = d.scratch + NOALLOC_SUM_OFF;
+	p.rows_pad = n_pad;
+	p.nb = nb;
+	p.block0 = 0;
+	p.nb_own = nb;
+	p.jt_total = n_pad / TJ;
+	p.n_pad = n_pad;
+	p.n_real = (unsigned)n;
+	p.counter = reinterpret_cast<unsigned*>(d.scratch);
+	p.pad_pos = 0.;
+	p.pos_rows = n_pad;	 // with one tile per block the walk names no tile past the last block
+	p.fx_e0 = 0;
+	// the same slicing rule as make_plan: enough units per resident CTA for a short tail
+	const unsigned slots = (unsigned)d.per_sm[prec == 64 ? 0 : 1] * (unsigned)d.n_sm;
+	const unsigned h_min = (nb & 1u) ? (nb - 1u) / 2u : nb / 2u - 1u;
+	const uint64_t pairs = sym_pair_evaluations((unsigned)n, nb, 1u, 0u, nb);
+	p.n_slices = choose_slices(nb, (1u + h_min) * (TJ / 32), slots, 0, MAX_SYM_SLICES,
+							   sym_units_per_slot((double)pairs, (unsigned)prec));
+	const unsigned long long units = (unsigned long long)nb * p.n_slices;
+	const unsigned grid = (unsigned)std::min<unsigned long long>(units, slots);
+	v.launch[0](dim3(grid), st, v.smem, p, eps * eps);
+	CK(cudaGetLastError());
+
+	NB_LAUNCH(noalloc_finish_kernel<T>, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st,
+			  d.scratch, (T*)acc_dev, (unsigned)n, n_pad, (T)(-(T)G));
+	CK(cudaGetLastError());
+	return NBODY_OK;
+}
+}  // namespace
+
+extern "C" int nbody_rhs_noalloc(int device, int precision, size_t n, const void* m_dev,
+								 const void* r4_dev, void* acc_dev, double grav_G, double eps,
+								 void* stream) {
+	nbody_ctx* ctx = nullptr;
+	if (precision != 64 && precision != 32)
+		return fail(ctx, NBODY_ERR_ARG, "nbody_rhs_noalloc: precision must be 64 or 32");
+	if (n > (size_t)NBODY_NOALLOC_MAX_BODIES)
+		return fail(ctx, NBODY_ERR_ARG,
+					"nbody_rhs_noalloc: n = " + std::to_string(n) + " exceeds NBODY_NOALLOC_MAX_BODIES = " +
+						std::to_string(NBODY_NOALLOC_MAX_BODIES) +
+						" (its working memory is a fixed array inside the library; use a context, "
+						"nbody_create + nbody_rhs, for larger systems)");
+	if (n == 0) return NBODY_OK;
+	if (!m_dev || !r4_dev || !acc_dev) return fail(ctx, NBODY_ERR_ARG, "nbody_rhs_noalloc: null array");
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+		return fail(ctx, NBODY_ERR_NO_DEVICE,
+					"no CUDA device: this library has no CPU fallback (sm_100a required)");
+	if (device < 0 || device >= ndev || device >= NOALLOC_MAX_DEVICES)
+		return fail(ctx, NBODY_ERR_ARG, "device index out of range");
+	CK(cudaSetDevice(device));
+	NoallocDev* d = nullptr;
+	const int rc = noalloc_setup(device, &d);
+	if (rc) return rc;
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	return precision == 64
+			   ? noalloc_enqueue<double>(*d, n, m_dev, r4_dev, acc_dev, grav_G, eps, st)
+			   : noalloc_enqueue<float>(*d, n, m_dev, r4_dev, acc_dev, grav_G, eps, st);
+}

@@ -731,3 +731,24 @@ def test_emulated_deterministic_on_several_ranks(oracle, world, owned_io):
         if base is None:
             base = res[0]["fin"]
         assert np.array_equal(base, res[0]["fin"])
+
+
+def test_emulated_abi_rhs_noalloc_calls_in_a_row(oracle):
+    """nbody_rhs_noalloc (the entry point for hosts that must not let the library allocate device
+    memory: its kernel works in a fixed array inside the library) under emulation, where a
+    "device" array is a host array: three calls in a row on different bodies share that array and
+    each one equals the oracle; sizes beyond the array are refused."""
+    for n, seed, prec, tol in ((600, 31, 64, 1e-12), (257, 32, 64, 1e-12), (300, 33, 32, 1e-4)):
+        dt = np.float64 if prec == 64 else np.float32
+        bodies = generators.uniform_bodies(n, seed=seed)
+        m = np.ascontiguousarray(bodies[:, 0], dtype=dt)
+        r4 = np.zeros((n, 4), dtype=dt)
+        r4[:, :3] = bodies[:, 1:4]
+        r4[:, 3] = 7.0      # ignored
+        acc = np.full((n, 3), np.nan, dtype=dt)
+        capi.rhs_noalloc(n, m.ctypes.data, r4.ctypes.data, acc.ctypes.data, precision=prec)
+        as_seen = np.column_stack([m, r4[:, :3], np.zeros((n, 3))]).astype(np.float64)
+        want = oracle.rhs(as_seen, threads=2)[:, 4:7]
+        assert rel_inf(acc, want) < tol, (n, prec)
+    with pytest.raises(capi.NBodyError, match="NBODY_NOALLOC_MAX_BODIES"):
+        capi.rhs_noalloc(capi.NOALLOC_MAX_BODIES + 1, 1, 1, 1)

@@ -108,6 +108,8 @@ inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t a, cudaEvent_t b)
 	return cudaSuccess;
 }
 inline cudaError_t cudaFuncSetAttribute(const void*, int, int) { return cudaSuccess; }
+// a `static __device__` array is an ordinary host array here: its "device address" is its address
+template <typename S> inline cudaError_t cudaGetSymbolAddress(void** p, const S& sym) { *p = (void*)&sym; return cudaSuccess; }
 inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int* n, const void*, int, size_t) {
 	*n = 2;
 	return cudaSuccess;
