@@ -117,6 +117,17 @@ int nbody_p2p_connect(nbody_ctx* ctx, const void* all_handles /* world x NBODY_P
 int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 					size_t* block_rows);
 
+/* Which build of the pair-symmetric kernel the automatic choice ("sym_variant" -1) runs for n
+ * bodies on `world` GPUs, as pure host arithmetic (no GPU needed): *variant = its index,
+ * *kernel_block_rows = the rows one thread block owns, *rank_block_rows = block_rows of
+ * nbody_partition.  On several GPUs the ranks own whole kernel blocks, so the choice always
+ * satisfies rank_block_rows % kernel_block_rows == 0 (the 256-row builds divide every per-rank
+ * block).  No counterpart in the reference (one kernel, BLOCK_SIZE fixed at 64, lab_5
+ * N_body.cu:29); lets a host -- and the CPU tests -- check a configuration before any rank
+ * enters a collective. */
+int nbody_sym_variant_for(size_t n, int precision, int world, int uniform_mass, int deterministic,
+						  int* variant, size_t* kernel_block_rows, size_t* rank_block_rows);
+
 /* G and eps captured by the RHS lambda (lab_4 .../struct_ode_system.hpp:34-36,53;
  * lab_5 N_body.cu:22,30).  Defaults 6.67e-11 and 1e-6. */
 int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab_5 #defines G (N_body.cu:30) */
@@ -134,8 +145,8 @@ int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab
  * n >= 2048 unless the peer-pull exchange is connected, the one-sided kernel below that.
  * On several GPUs the ranks split the blocks of one global schedule and the sums are
  * reduce-scattered (NCCL exchange only; with "sym_variant" -1 a kernel variant is chosen whose
- * block divides the per-rank block of nbody_partition, a forced variant that does not is
- * NBODY_ERR_STATE).  nbody_timing.pair_symmetry reports which kernel ran),
+ * block divides the per-rank block of nbody_partition -- one always exists, see
+ * nbody_sym_variant_for -- a forced variant that does not is NBODY_ERR_STATE).  nbody_timing.pair_symmetry reports which kernel ran),
  * "sym_variant" (kernel variant id of that mode, -1 = default),
  * "deterministic" (0 default / 1; set before the upload): the pair-symmetric kernel adds every
  * unit's share of a row as an exact FIXED-POINT integer (192-bit window derived from n, the
@@ -143,7 +154,14 @@ int nbody_set_params(nbody_ctx* ctx, double grav_G, double eps); /* not "G": lab
  * kernel rounds each row sum to T once: BIT-REPRODUCIBLE run to run whatever the scheduling, on
  * any number of GPUs (the reduce-scatter sums integers), same tolerances against the reference.
  * NBODY_ERR_STATE from the step / RHS call if eps == 0 or the input's dynamic range does not fit
- * the window.  No effect where the one-sided kernel runs (it is bit-reproducible as it is).
+ * the window.  The window is FIXED from the state at upload (masses, bounding box): every
+ * contribution is truncated at an absolute 2^e0 (e0 = log2(n m_max / eps^2) - 190), and the check
+ * that 60 bits remain under the smallest pair term m_min / D^2 is made against the bounding box
+ * D of the UPLOADED positions only.  Bodies that leave that box during a long run (Plummer
+ * escapers) keep bit-reproducible sums, but the precision floor is then the absolute 2^e0, not the
+ * 60 relative bits; it is not re-derived after nbody_step_undo or an adaptive step either --
+ * upload again to re-derive it.  No effect where the one-sided kernel runs (it is bit-reproducible
+ * as it is).
  * nbody_timing.deterministic reports what the kernel in use guarantees). */
 int nbody_set_option(nbody_ctx* ctx, const char* name, long value);
 

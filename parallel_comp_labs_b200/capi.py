@@ -115,6 +115,8 @@ def _bind(L: C.CDLL) -> C.CDLL:
     L.nbody_host_free.argtypes = [vp]
     L.nbody_host_free.restype = None
     L.nbody_measure_fma_peak.argtypes = [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_double)]
+    L.nbody_sym_variant_for.argtypes = [sz, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int),
+                                        C.POINTER(sz), C.POINTER(sz)]
     if hasattr(L, "nbody_rhs_noalloc"):
         L.nbody_rhs_noalloc.argtypes = [C.c_int, C.c_int, sz, vp, vp, vp, C.c_double, C.c_double, vp]
     return L
@@ -134,6 +136,16 @@ def partition(n: int, world: int, rank: int):
     if lib().nbody_partition(n, world, rank, C.byref(b), C.byref(e), C.byref(blk)):
         raise ValueError(lib().nbody_last_error(None).decode())
     return b.value, e.value, blk.value
+
+
+def sym_variant_for(n: int, precision: int = 64, world: int = 1, uniform_mass: bool = True,
+                    deterministic: bool = False):
+    """(variant, kernel_block_rows, rank_block_rows) of the automatic pair-symmetric choice."""
+    v, kb, rb = C.c_int(), C.c_size_t(), C.c_size_t()
+    if lib().nbody_sym_variant_for(n, precision, world, int(uniform_mass), int(deterministic),
+                                   C.byref(v), C.byref(kb), C.byref(rb)):
+        raise ValueError(lib().nbody_last_error(None).decode())
+    return v.value, kb.value, rb.value
 
 
 def nccl_unique_id() -> bytes:

@@ -346,28 +346,37 @@ const Variant& variant_of(const nbody_ctx* c) {
 //   FP32 equal masses   N >= 16k: 1 (I=8, shuffled j);  general masses: 5 (64 threads, I=8, re-read j);  N <= 12k: 3
 // On several GPUs the size that matters is the per-rank share of the pairs: n / sqrt(world).
 // Option "deterministic" = 1 then swaps the choice for its fixed-point twin (same block size).
-const SymVariant& sym_variant_of(const nbody_ctx* c) {
-	const int nv = c->prec == 64 ? N_SYM64 : N_SYM32;
-	const SymVariant* tab = c->prec == 64 ? g_sym64 : g_sym32;
-	const int* twin = c->prec == 64 ? g_sym64_fx_twin : g_sym32_fx_twin;
-	const bool det = c->opt_deterministic != 0;
-	long v = c->opt_sym_variant;
-	if (v >= 0 && v < nv) return tab[det ? twin[v] : v];
-	const double n_eff = (double)c->n / std::sqrt((double)c->world);
+// (pure host arithmetic on the numbers that decide: nbody_sym_variant_for exposes it to the tests)
+// Several GPUs: every list is followed by a 256-row build (FP64 entry 10, FP32 entry 2; their
+// fixed-point twins 15 and 9) -- nbody_partition pads the per-rank block to 256 rows only, so when
+// that block is an odd multiple of 256 (n = 1 100 000 on 2 GPUs) no 512- or 1024-row build fits and
+// the 256-row one is what runs, instead of the call failing.
+const SymVariant& sym_variant_pick(int prec, size_t n, int world, unsigned own_pad, bool unimass,
+								   bool det, long forced) {
+	const int nv = prec == 64 ? N_SYM64 : N_SYM32;
+	const SymVariant* tab = prec == 64 ? g_sym64 : g_sym32;
+	const int* twin = prec == 64 ? g_sym64_fx_twin : g_sym32_fx_twin;
+	if (forced >= 0 && forced < nv) return tab[det ? twin[forced] : forced];
+	const double n_eff = (double)n / std::sqrt((double)world);
 	// per-size winners of profiles/r02_sym_crossover.md and r02_sym_sweep3.md
 	static const int p64_small[] = {3, 3, 3}, p64_mid[] = {5, 3, 3}, p64_fine[] = {9, 5, 3},
 					 p64_um[] = {8, 9, 5}, p64_gen[] = {7, 9, 5}, p32_small[] = {3, 2, 2},
 					 p32_um[] = {1, 3, 2}, p32_gen[] = {5, 3, 2};
 	const int* pref;
-	if (c->prec == 32) pref = n_eff < 14000 ? p32_small : c->unimass ? p32_um : p32_gen;
+	if (prec == 32) pref = n_eff < 14000 ? p32_small : unimass ? p32_um : p32_gen;
 	else if (n_eff < 10000) pref = p64_small;
-	else if (c->unimass) pref = n_eff < 26000 ? p64_mid : n_eff < 400000 ? p64_fine : p64_um;
-	else pref = n_eff < 50000 ? p64_mid : (n_eff < 500000 || c->world > 1) ? p64_fine : p64_gen;
+	else if (unimass) pref = n_eff < 26000 ? p64_mid : n_eff < 400000 ? p64_fine : p64_um;
+	else pref = n_eff < 50000 ? p64_mid : (n_eff < 500000 || world > 1) ? p64_fine : p64_gen;
 	for (int k = 0; k < 3; ++k) {
 		const SymVariant& sv = tab[det ? twin[pref[k]] : pref[k]];
-		if (c->world == 1 || c->own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
+		if (world == 1 || own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
 	}
-	return tab[det ? twin[pref[2]] : pref[2]];
+	const int fits_all = prec == 64 ? 10 : 2;  // 256-row builds: divide every per-rank block
+	return tab[det ? twin[fits_all] : fits_all];
+}
+const SymVariant& sym_variant_of(const nbody_ctx* c) {
+	return sym_variant_pick(c->prec, c->n, c->world, c->own_pad, c->unimass,
+							c->opt_deterministic != 0, c->opt_sym_variant);
 }
 
 // Window of the fixed-point row sums (fixed_sums.cuh): the top comes from a rigorous bound on any
@@ -1216,6 +1225,22 @@ int nbody_partition(size_t n, int world, int rank, size_t* begin, size_t* end,
 	*begin = b;
 	*end = std::min(n, blk * (size_t)(rank + 1));
 	*block_rows = blk;
+	return NBODY_OK;
+}
+
+int nbody_sym_variant_for(size_t n, int precision, int world, int uniform_mass, int deterministic,
+						  int* variant, size_t* kernel_block_rows, size_t* rank_block_rows) {
+	nbody_ctx* ctx = nullptr;
+	if ((precision != 64 && precision != 32) || !variant || !kernel_block_rows || !rank_block_rows)
+		return fail(ctx, NBODY_ERR_ARG, "nbody_sym_variant_for: bad argument");
+	size_t b = 0, e = 0, blk = 0;
+	const int rc = nbody_partition(n, world, 0, &b, &e, &blk);
+	if (rc) return rc;
+	const SymVariant& sv = sym_variant_pick(precision, n, world, (unsigned)blk, uniform_mass != 0,
+											deterministic != 0, -1);
+	*variant = (int)(&sv - (precision == 64 ? g_sym64 : g_sym32));
+	*kernel_block_rows = (size_t)(sv.threads * sv.ipt);
+	*rank_block_rows = blk;
 	return NBODY_OK;
 }
 

@@ -244,3 +244,34 @@ def test_cxx_tableaux_match_python_table():
         assert tableaux.check_order_conditions(name) < 1e-14
         seen.add(name)
     assert seen == set(tableaux.TABLEAUX)
+
+
+def test_automatic_pair_symmetric_build_divides_every_rank_block():
+    """Several GPUs: the ranks own whole kernel blocks, and nbody_partition pads a rank's block to
+    256 rows only -- so whatever n and world, the automatic choice must name a build whose block
+    divides it (round 2 chose 512-/1024-row builds from preference lists that could all miss:
+    n = 1 100 000 on 2 GPUs, n = 2 000 000 on 8, n = 1 000 960 on 2 failed with NBODY_ERR_STATE)."""
+    named = [(1_100_000, 2), (2_000_000, 8), (1_000_960, 2)]
+    rng = np.random.default_rng(5)
+    sizes = [int(x) for x in rng.integers(2048, 3_000_000, 300)] + [2048, 20_000, 262_144, 1 << 20]
+    cases = named + [(n, w) for n in sizes for w in (1, 2, 3, 4, 8)]
+    fallback_seen = False
+    for n, world in cases:
+        for prec in (64, 32):
+            for um in (True, False):
+                for det in (False, True):
+                    v, kb, rb = capi.sym_variant_for(n, prec, world, um, det)
+                    assert rb % 256 == 0 and kb % 256 == 0
+                    assert world == 1 or rb % kb == 0, (n, world, prec, um, det, v, kb, rb)
+                    fallback_seen |= world > 1 and kb == 256 and (rb // 256) % 2 == 1 and n > 800_000
+    assert fallback_seen            # the named cases do end on a 256-row build
+    # one GPU: the measured winners are untouched (profiles/r02_sym_sweep2.md, r02_sym_crossover.md)
+    assert capi.sym_variant_for(1 << 20, 64, 1, True)[0] == 8
+    assert capi.sym_variant_for(1 << 20, 64, 1, False)[0] == 7
+    assert capi.sym_variant_for(262_144, 64, 1, True)[0] == 9
+    assert capi.sym_variant_for(20_000, 64, 1, True)[0] == 5
+    assert capi.sym_variant_for(3000, 64, 1, True)[0] == 3
+    assert capi.sym_variant_for(1 << 20, 32, 1, True)[0] == 1
+    assert capi.sym_variant_for(1 << 20, 64, 1, True, deterministic=True)[0] == 11
+    with pytest.raises(ValueError):
+        capi.sym_variant_for(4, 64, 5)
