@@ -190,8 +190,10 @@ def run_reference(args):
         "cpu_baseline": dict(info, value=value),
         "e2e": {"value": value, "unit": "G interactions/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
-        "note": "reference CPU path (lab_4) on host cores; ms_per_step is the time a full "
-                "step of this workload would take at the sampled rate",
+        "extrapolated_from_rows": True,
+        "note": "reference CPU path (lab_4) on host cores, timed on a bounded ROW SAMPLE of one RK "
+                "stage's RHS (cpu_baseline.sample); ms_per_step is NOT a measured step: it is the time "
+                "a full step of this workload would take at the sampled rate",
     }
     print(json.dumps(line), flush=True)
 
@@ -485,6 +487,9 @@ def run_b200(args):
                                  "fp64_instr_per_pair": None,
                                  "fp64_instr_per_pair_evaluation":
                                      (18 if tm.uniform_mass else 20) if args.precision == 64 else None})
+        archived = archived_ncu(args.n, world, args.precision, bool(tm.pair_symmetry),
+                                bool(tm.uniform_mass),
+                                int(tm.sym_variant) if tm.pair_symmetry else int(tm.variant))
         line = {
             "metric": "G body-interactions/s", "value": value, "unit": "G interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -499,12 +504,11 @@ def run_b200(args):
             "roofline": {
                 "bound": "fp64_fma_pipe" if args.precision == 64 else "fp32_fma_pipe",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": TRAFFIC_BYTES_PER_LAUNCH.get((args.n, world, args.precision,
-                                                         bool(tm.pair_symmetry))),
+                "traffic": archived["traffic"],
+                "traffic_source": archived["traffic_source"],
                 "algorithmic_bytes_per_launch": int(n * 4 * np.dtype(dtype).itemsize
                                                     + (e - b) * 3 * np.dtype(dtype).itemsize),
-                "pipe_util_ncu": PIPE_UTIL_NCU.get((args.precision, bool(tm.pair_symmetry),
-                                                    bool(tm.uniform_mass))),
+                "pipe_util_ncu_archived": archived["pipe_util"],
                 "kernel": "nbody::force_sym_kernel" if tm.pair_symmetry else "nbody::force_kernel",
                 "mean_launch_ms": mean_force_ms,
                 "evaluated_pairs_per_delivered_interaction":
@@ -540,30 +544,46 @@ def run_b200(args):
         raise SystemExit(f"PARITY FAILED: {parity}")
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed
-# `ncu --set full` captures under profiles/ (key: n, gpus, precision); None = not captured.
-# Key: (n, gpus, precision, pair-symmetric kernel?)
-TRAFFIC_BYTES_PER_LAUNCH = {
-    (1 << 20, 1, 64, False): 83091968 + 963913216,   # profiles/r01_force_kernel_1M_ncu_full.csv
-    (1 << 20, 1, 64, True): 58879744 + 550656,       # profiles/r02_ncu_k1s_fp64_equal_1M.csv
-    (1 << 18, 1, 64, True): 14749184 + 11520,        # profiles/r02_ncu_k1s_fp64_equal_262144.csv
-    (1 << 18, 1, 32, True): 7392768 + 0,             # profiles/r02_ncu_k1s_fp32_262144.csv
+# ARCHIVED profiler readings of the dominant kernel, from the committed `ncu --set full` captures
+# under profiles/ -- ncu cannot run inside a timed bench, so these are NOT measurements of this run.
+# A line carries them only when the run is the captured configuration: same n, one GPU, same
+# precision, same kernel and kernel variant, same mass mode; anything else gets null.
+#   traffic   = dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch
+#   pipe_util = sm__inst_executed_pipe_fp64 / _fma .avg.pct_of_peak_sustained_active
+# key: (n, gpus, precision, pair-symmetric kernel?, equal masses?, variant index)
+ARCHIVED_NCU = {
+    (1 << 20, 1, 64, False, True, 0): {"traffic": 83091968 + 963913216, "pipe_util": 0.8974,
+                                       "source": "profiles/r01_force_kernel_1M_ncu_full.csv"},
+    (1 << 20, 1, 64, True, True, 8): {"traffic": 58879744 + 550656, "pipe_util": 0.8377,
+                                      "source": "profiles/r02_ncu_k1s_fp64_equal_1M.csv"},
+    (1 << 18, 1, 64, True, True, 9): {"traffic": 14749184 + 11520, "pipe_util": None,
+                                      "source": "profiles/r02_ncu_k1s_fp64_equal_262144.csv"},
+    (1 << 18, 1, 64, True, False, 5): {"traffic": None, "pipe_util": 0.8248,
+                                       "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv"},
+    (1 << 18, 1, 32, True, True, 1): {"traffic": 7392768 + 0, "pipe_util": 0.6923,
+                                      "source": "profiles/r02_ncu_k1s_fp32_262144.csv",
+                                      "note": "issue-bound: 83 % of issue slots"},
+    (20000, 1, 64, False, False, 0): {"traffic": None, "pipe_util": 0.8195,
+                                      "source": "profiles/r02_ncu_k1_fp64_general_20000.csv"},
+    (131072, 1, 32, False, True, 0): {"traffic": None, "pipe_util": 0.7031,
+                                      "source": "profiles/r02_ncu_k1_fp32_131072.csv"},
 }
 
-# FMA-pipe utilisation of the dominant kernel from the committed ncu captures
-# (sm__inst_executed_pipe_fp64 / sm__inst_executed_pipe_fma .avg.pct_of_peak_sustained_active);
-# key: (precision, pair-symmetric kernel?, equal masses?)
-PIPE_UTIL_NCU = {
-    (64, True, True): {"value": 0.8377, "source": "profiles/r02_ncu_k1s_fp64_equal_1M.csv",
-                       "captured_sym_variant": 8},
-    (64, True, False): {"value": 0.8248, "source": "profiles/r02_ncu_k1s_fp64_general_262144.csv",
-                        "captured_sym_variant": 5},
-    (32, True, True): {"value": 0.6923, "source": "profiles/r02_ncu_k1s_fp32_262144.csv",
-                       "captured_sym_variant": 1, "note": "issue-bound: 83 % of issue slots"},
-    (64, False, True): {"value": 0.8974, "source": "profiles/r01_force_kernel_1M_ncu_full.csv"},
-    (64, False, False): {"value": 0.8195, "source": "profiles/r02_ncu_k1_fp64_general_20000.csv (N = 20k)"},
-    (32, False, True): {"value": 0.7031, "source": "profiles/r02_ncu_k1_fp32_131072.csv"},
-}
+
+def archived_ncu(n, gpus, precision, sym, unimass, variant):
+    hit = ARCHIVED_NCU.get((n, gpus, precision, sym, unimass, variant))
+    if hit is None:
+        return {"traffic": None, "pipe_util": None,
+                "traffic_source": "no committed ncu capture of this configuration (n, GPUs, precision, "
+                                  "kernel variant, mass mode); ncu cannot run inside a timed bench"}
+    pu = None
+    if hit["pipe_util"] is not None:
+        pu = {"value": hit["pipe_util"], "source": hit["source"], "captured_variant": variant,
+              "captured_n": n, "live": False}
+        if "note" in hit:
+            pu["note"] = hit["note"]
+    return {"traffic": hit["traffic"], "pipe_util": pu,
+            "traffic_source": "archived, not live: " + hit["source"]}
 
 
 if __name__ == "__main__":
