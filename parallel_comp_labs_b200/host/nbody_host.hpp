@@ -24,6 +24,7 @@
 #include <cstring>
 #include <deque>
 #include <fstream>
+#include <functional>
 #include <iostream>
 #include <memory>
 #include <mutex>
@@ -615,6 +616,34 @@ class Solver_N_body {
 	}
 
    private:
+	// Several ranks, one of them fails: its peers may already be blocked in a collective that it
+	// will never join, so the process has to end (a join() would hang).  What rank 0 has written so
+	// far must not be lost with it: rank 0 registers how to flush its open sinks, and whichever rank
+	// ends the process runs that first (std::_Exit itself flushes nothing and runs no destructors).
+	std::mutex abort_mu_;
+	std::function<void()> abort_flush_;
+	struct AbortFlushScope {  // registration that ends with rank 0's sinks
+		Solver_N_body* s;
+		AbortFlushScope(Solver_N_body* s_, std::function<void()> f) : s(s_) {
+			std::lock_guard<std::mutex> g(s->abort_mu_);
+			s->abort_flush_ = std::move(f);
+		}
+		~AbortFlushScope() {
+			std::lock_guard<std::mutex> g(s->abort_mu_);
+			s->abort_flush_ = nullptr;
+		}
+	};
+	[[noreturn]] void abort_world(int rank, const std::string& error) {
+		std::cerr << "rank " << rank << ": " << error << std::endl;
+		{
+			std::lock_guard<std::mutex> g(abort_mu_);
+			if (abort_flush_) abort_flush_();
+		}
+		std::cout.flush();
+		std::fflush(nullptr);
+		std::_Exit(3);
+	}
+
 	void rank_main(ode_system<T>& sys, const RunOptions& opt, int rank, int world,
 				   const char* uid, std::string& error) {
 		const std::size_t n = sys.traj_init.size();
@@ -622,20 +651,12 @@ class Solver_N_body {
 		const int prec = std::is_same<T, double>::value ? 64 : 32;
 		if (nbody_create(&ctx, n, prec, rank, rank, world, world > 1 ? uid : nullptr) != NBODY_OK) {
 			error = std::string("nbody_create: ") + nbody_last_error(nullptr);
-			if (world > 1) {  // peers are waiting in ncclCommInitRank for this rank
-				std::cerr << "rank " << rank << ": " << error << std::endl;
-				std::_Exit(3);
-			}
+			if (world > 1) abort_world(rank, error);  // peers are waiting in ncclCommInitRank
 			return;
 		}
 		auto fail = [&](const char* what) {
 			error = std::string(what) + ": " + nbody_last_error(ctx);
-			if (world > 1) {
-				// peers may already be blocked in a collective that this rank will never join:
-				// report and end the process instead of hanging in join()
-				std::cerr << "rank " << rank << ": " << error << std::endl;
-				std::_Exit(3);
-			}
+			if (world > 1) abort_world(rank, error);  // never leave the peers waiting (see abort_world)
 			nbody_destroy(ctx);
 		};
 		if (nbody_set_params(ctx, (double)sys.G, (double)sys.eps)) return fail("set_params");
@@ -656,12 +677,15 @@ class Solver_N_body {
 		}
 		auto fail_io = [&](const std::string& why) {	// as `fail`: never leave the peers waiting
 			error = why;
-			if (world > 1) {
-				std::cerr << "rank " << rank << ": " << error << std::endl;
-				std::_Exit(3);
-			}
+			if (world > 1) abort_world(rank, error);
 			nbody_destroy(ctx);
 		};
+		std::unique_ptr<AbortFlushScope> abort_scope;
+		if (rank == 0 && world > 1)
+			abort_scope.reset(new AbortFlushScope(this, [&traj, &sinks] {
+				if (traj.is_open()) traj.flush();
+				sinks.finish();
+			}));
 		if (rank == 0 && !opt.traj_bin_path.empty() && !sinks.open_bin(opt.traj_bin_path, n, opt.flavour))
 			return fail_io("cannot open " + opt.traj_bin_path);
 		std::string why;

@@ -752,3 +752,21 @@ def test_emulated_abi_rhs_noalloc_calls_in_a_row(oracle):
         assert rel_inf(acc, want) < tol, (n, prec)
     with pytest.raises(capi.NBodyError, match="NBODY_NOALLOC_MAX_BODIES"):
         capi.rhs_noalloc(capi.NOALLOC_MAX_BODIES + 1, 1, 1, 1)
+
+
+def test_emulated_cxx_driver_failing_rank_keeps_what_was_written(emulated_driver, golden, tmp_path):
+    """Two rank threads and a step that fails (fixed-point sums refuse eps = 0): the ranks cannot
+    be joined -- a peer may sit in a collective -- so the process ends with status 3, but the rows
+    rank 0 had already handed to its sinks (header and the t_start row) are flushed first."""
+    inp = str(tmp_path / "4body.txt")
+    _write_input(inp, golden["body4"])
+    traj = str(tmp_path / "traj_fail.csv")
+    r = subprocess.run([emulated_driver, "--system", "default_test", "--input", inp, "--tau", "0.1",
+                        "--t-final", "20", "--max-steps", "3", "--traj-out", traj, "--gpus", "2",
+                        "--pair-symmetry", "1", "--deterministic", "--eps", "0",
+                        "--timing-out", str(tmp_path / "timing.csv")],
+                       capture_output=True, text=True, env=dict(os.environ), timeout=120)
+    assert r.returncode == 3, (r.returncode, r.stderr)
+    assert "eps > 0" in r.stderr
+    lines = open(traj).read().splitlines()
+    assert len(lines) == 2 and lines[0].startswith("t") and lines[1].startswith("0")
