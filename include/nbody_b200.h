@@ -10,7 +10,10 @@
  * Each entry point cites the reference interface it replaces (file:line relative to
  * the reference repository root).  One context == one GPU == one "rank"
  * (the MPI rank of lab_4).  A context is not thread-safe; distinct contexts may be
- * driven from distinct threads or processes.
+ * driven from distinct threads or processes.  ONE exception, made for the trajectory writer:
+ * nbody_snapshot_wait and nbody_snapshot_release may be called from one other thread while the
+ * thread that drives the context is inside any other call (they share only the snapshot slot
+ * table, which is atomic); on that thread their error text is nbody_last_error(NULL).
  *
  * Body layouts accepted at the boundary
  *   AoS  Body<T> {T m; T r[3]; T v[3];}            lab_4 .../struct_Body.hpp:5-10
@@ -234,7 +237,8 @@ int nbody_step_undo(nbody_ctx* ctx);
  * may take snapshots, as rank 0 alone writes rows in the reference.  nbody_snapshot_wait
  * blocks until that copy has landed and returns the pinned pointer, valid until
  * nbody_snapshot_release.  The ring has NBODY_SNAPSHOT_SLOTS slots; asking for a
- * snapshot while all are held is NBODY_ERR_STATE. */
+ * snapshot while all are held is NBODY_ERR_STATE.  _wait / _release: callable from a second
+ * thread, see the threading note at the top; their errors go to nbody_last_error(NULL). */
 #define NBODY_SNAPSHOT_SLOTS 4
 int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket);
 int nbody_snapshot_wait(nbody_ctx* ctx, uint64_t ticket, const void** r_host);

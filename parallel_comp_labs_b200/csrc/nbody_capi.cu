@@ -16,6 +16,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -242,8 +243,12 @@ struct nbody_ctx {
 	void* snap_dev[NBODY_SNAPSHOT_SLOTS] = {};
 	void* snap_host[NBODY_SNAPSHOT_SLOTS] = {};
 	cudaEvent_t snap_ev[NBODY_SNAPSHOT_SLOTS] = {};
-	int snap_state[NBODY_SNAPSHOT_SLOTS] = {};	// 0 free, 1 in flight / held
-	uint64_t snap_ticket[NBODY_SNAPSHOT_SLOTS] = {};
+	// nbody_snapshot_wait / _release may run on ONE other thread (the trajectory writer) while the
+	// integrator thread is inside any other call: the slot table is the only state they share.
+	// A slot is published by the release-store of snap_state (after its ticket, event and buffers
+	// are in place) and given back by the release-store of 0.
+	std::atomic<int> snap_state[NBODY_SNAPSHOT_SLOTS] = {};	 // 0 free, 1 in flight / held
+	std::atomic<uint64_t> snap_ticket[NBODY_SNAPSHOT_SLOTS] = {};
 	uint64_t next_ticket = 1;
 	cudaStream_t sc = nullptr, sm = nullptr, sx = nullptr;
 	cudaEvent_t e_gy = nullptr;	 // completion of the eager end-of-step gather of Y
@@ -1899,7 +1904,7 @@ int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
 	CK(cudaSetDevice(ctx->device));
 	int slot = -1;
 	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s)
-		if (!ctx->snap_state[s]) { slot = s; break; }
+		if (!ctx->snap_state[s].load(std::memory_order_acquire)) { slot = s; break; }
 	if (slot < 0) return fail(ctx, NBODY_ERR_STATE, "all snapshot slots are held");
 	const size_t bytes = ctx->n * 3 * ctx->esz;
 	if (!ctx->snap_dev[0]) {  // first snapshot: set the whole ring up at once
@@ -1925,33 +1930,41 @@ int nbody_snapshot_async(nbody_ctx* ctx, uint64_t* ticket) {
 	CK(cudaMemcpyAsync(ctx->snap_host[slot], ctx->snap_dev[slot], bytes, cudaMemcpyDeviceToHost,
 					   ctx->sx));
 	CK(cudaEventRecord(ctx->snap_ev[slot], ctx->sx));
-	ctx->snap_state[slot] = 1;
-	ctx->snap_ticket[slot] = ctx->next_ticket++;
-	*ticket = ctx->snap_ticket[slot];
+	const uint64_t tk = ctx->next_ticket++;
+	ctx->snap_ticket[slot].store(tk, std::memory_order_relaxed);
+	ctx->snap_state[slot].store(1, std::memory_order_release);
+	*ticket = tk;
 	return NBODY_OK;
 }
 
 static int find_slot(nbody_ctx* ctx, uint64_t ticket) {
 	for (int s = 0; s < NBODY_SNAPSHOT_SLOTS; ++s)
-		if (ctx->snap_state[s] && ctx->snap_ticket[s] == ticket) return s;
+		if (ctx->snap_state[s].load(std::memory_order_acquire) &&
+			ctx->snap_ticket[s].load(std::memory_order_relaxed) == ticket)
+			return s;
 	return -1;
 }
 
-int nbody_snapshot_wait(nbody_ctx* ctx, uint64_t ticket, const void** r_host) {
-	if (!ctx || !r_host) return fail(ctx, NBODY_ERR_ARG, "null argument");
-	const int s = find_slot(ctx, ticket);
+// These two may be called from a second thread (see nbody_ctx::snap_state).  They touch the slot
+// table only, and report errors through the calling thread's own message (nbody_last_error(NULL)):
+// the context's message string belongs to the thread that drives the context.
+int nbody_snapshot_wait(nbody_ctx* owner, uint64_t ticket, const void** r_host) {
+	nbody_ctx* ctx = nullptr;  // what fail / CK write to: the thread-local message only
+	if (!owner || !r_host) return fail(ctx, NBODY_ERR_ARG, "null argument");
+	const int s = find_slot(owner, ticket);
 	if (s < 0) return fail(ctx, NBODY_ERR_ARG, "unknown snapshot ticket");
-	CK(cudaEventSynchronize(ctx->snap_ev[s]));
-	*r_host = ctx->snap_host[s];
+	CK(cudaEventSynchronize(owner->snap_ev[s]));
+	*r_host = owner->snap_host[s];
 	return NBODY_OK;
 }
 
-int nbody_snapshot_release(nbody_ctx* ctx, uint64_t ticket) {
-	if (!ctx) return fail(ctx, NBODY_ERR_ARG, "null context");
-	const int s = find_slot(ctx, ticket);
+int nbody_snapshot_release(nbody_ctx* owner, uint64_t ticket) {
+	nbody_ctx* ctx = nullptr;
+	if (!owner) return fail(ctx, NBODY_ERR_ARG, "null context");
+	const int s = find_slot(owner, ticket);
 	if (s < 0) return fail(ctx, NBODY_ERR_ARG, "unknown snapshot ticket");
-	CK(cudaEventSynchronize(ctx->snap_ev[s]));
-	ctx->snap_state[s] = 0;
+	CK(cudaEventSynchronize(owner->snap_ev[s]));
+	owner->snap_state[s].store(0, std::memory_order_release);
 	return NBODY_OK;
 }
 

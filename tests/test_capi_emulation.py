@@ -764,7 +764,9 @@ def test_emulated_cxx_driver_failing_rank_keeps_what_was_written(emulated_driver
     r = subprocess.run([emulated_driver, "--system", "default_test", "--input", inp, "--tau", "0.1",
                         "--t-final", "20", "--max-steps", "3", "--traj-out", traj, "--gpus", "2",
                         "--pair-symmetry", "1", "--deterministic", "--eps", "0",
-                        "--timing-out", str(tmp_path / "timing.csv")],
+                        # --report: an energy all-reduce before the loop, so that neither rank reaches
+                        # the failing step before rank 0 has written its first row
+                        "--report", "--timing-out", str(tmp_path / "timing.csv")],
                        capture_output=True, text=True, env=dict(os.environ), timeout=120)
     assert r.returncode == 3, (r.returncode, r.stderr)
     assert "eps > 0" in r.stderr
