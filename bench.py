@@ -218,7 +218,7 @@ def workload_config(args, tau, eps, variant):
 
 
 # ---------------------------------------------------------------- post-run parity (checker only)
-def parity_block(ctx, bodies, eps, precision, rows_per_run=32, runs=4):
+def parity_block(ctx, bodies, eps, precision, rows_per_run=32, runs=4, tau=None):
     """After the timed region: this rank evaluates one RHS of the bench's initial state through
     the library and checks `runs` x `rows_per_run` of ITS OWNED rows against the oracle (the
     reference's begin,end API, struct_ode_system.hpp:53-57: rows [b,e) against all N bodies).
@@ -232,10 +232,10 @@ def parity_block(ctx, bodies, eps, precision, rows_per_run=32, runs=4):
     got = ctx.rhs().astype(np.float64)
     b, e = ctx.owned_range()
     own = e - b
-    if own <= 0:
-        return 0, 0.0, 0.0
-    rows_per_run = min(rows_per_run, own)
-    starts = sorted({b + int(k * (own - rows_per_run) / max(runs - 1, 1)) for k in range(runs)})
+    rows_per_run = max(0, min(rows_per_run, own))
+    # (a rank that owns no rows checks nothing but still takes part in the collectives below)
+    starts = (sorted({b + int(k * (own - rows_per_run) / max(runs - 1, 1)) for k in range(runs)})
+              if own > 0 else [])
     worst_norm = worst_row = 0.0
     ref64 = np.ascontiguousarray(bodies.astype(dtype), dtype=np.float64)  # the values the GPU holds
     for s0 in starts:
@@ -244,9 +244,32 @@ def parity_block(ctx, bodies, eps, precision, rows_per_run=32, runs=4):
         worst_norm = max(worst_norm, float(np.abs(g - want).max() / np.abs(want).max()))
         worst_row = max(worst_row, float((np.abs(g - want).max(axis=1)
                                           / np.maximum(np.abs(want).max(axis=1), 1e-300)).max()))
+    PARITY_EXTRA.clear()
+    if tau is not None:
+        # One 1-stage step (Euler, through nbody_step_tableau: the fused stage kernel, the end-of-step
+        # exchange of Y on several GPUs) and a second RHS on the stepped, gathered state:
+        #   y1 = y0 + tau f(y0): sampled owned rows against y0 and the oracle rows computed above;
+        #   f(y1): the same rows against the oracle evaluated on the DOWNLOADED y1 (all N bodies).
+        ctx.step_tableau([], [1.0], 1.0, tau, 1, sync=True)
+        y1 = ctx.download_aos().astype(np.float64)      # collective: every rank calls parity_block
+        got2 = ctx.rhs().astype(np.float64)
+        st_err = dv_err = r2_err = 0.0
+        for s0 in starts:
+            sl = slice(s0, s0 + rows_per_run)
+            a0 = o.rhs(ref64, s0, s0 + rows_per_run, eps=eps, threads=2)[sl, 4:7]
+            want_r = ref64[sl, 1:4] + tau * ref64[sl, 4:7]
+            want_v = ref64[sl, 4:7] + tau * a0
+            st_err = max(st_err, float(np.abs(y1[sl, 1:4] - want_r).max() / np.abs(want_r).max()),
+                         float(np.abs(y1[sl, 4:7] - want_v).max() / np.abs(want_v).max()))
+            dv_err = max(dv_err, float(np.abs((y1[sl, 4:7] - ref64[sl, 4:7]) - tau * a0).max()
+                                       / np.abs(tau * a0).max()))
+            want2 = o.rhs(y1, s0, s0 + rows_per_run, eps=eps, threads=2)[sl, 4:7]
+            r2_err = max(r2_err, float(np.abs(got2[sl] - want2).max() / np.abs(want2).max()))
+        PARITY_EXTRA.update(state_rel_err=st_err, dv_rel_err=dv_err, rhs2_rel_err=r2_err)
     return len(starts) * rows_per_run, worst_norm, worst_row
 
 
+PARITY_EXTRA = {}     # filled by parity_block(tau=...): state after one Euler step, second RHS
 PARITY_TOL = {64: (1e-12, 1e-10), 32: (1e-4, 2e-3)}     # (norm-relative, per-row) -- tests/ hold the same
 
 
@@ -400,14 +423,26 @@ def run_b200(args):
     # ---- parity of THIS run's configuration (every rank checks rows it owns; not timed) -------
     parity = None
     if not args.no_parity:
-        prow, pnorm, pper = parity_block(ctx, bodies, eps, args.precision)
+        prow, pnorm, pper = parity_block(ctx, bodies, eps, args.precision, tau=tau)
+        extra = {k: max_over_ranks(v) for k, v in sorted(PARITY_EXTRA.items())}
         tol_norm, tol_row = PARITY_TOL[args.precision]
+        tol_state = 1e-10 if args.precision == 64 else 1e-4      # north_star's trajectory tolerance
         parity = {"rows": int(sum_over_ranks(float(prow))), "rows_per_rank": int(prow),
                   "rhs_rel_err": max_over_ranks(pnorm), "per_row_max": max_over_ranks(pper),
                   "tolerance": {"rhs_rel_err": tol_norm, "per_row": tol_row},
                   "checker": "oracle/nbody_oracle.c (bit-exact restatement of lab_4 N_body_func), "
                              "rows [b,e) of each rank's owned block against all N bodies"}
         parity["ok"] = bool(parity["rhs_rel_err"] < tol_norm and parity["per_row_max"] < tol_row)
+        if extra:
+            # (dv_rel_err is reported, not gated: v1 - v0 cancels, its floor is eps_mach |v| / |tau a|)
+            parity.update(extra)
+            parity["after_one_euler_step"] = ("state_rel_err: positions / velocities of sampled owned rows "
+                                              "after y1 = y0 + tau f(y0) (nbody_step_tableau, 1 stage); "
+                                              "dv_rel_err: their velocity increments against tau x oracle rows; "
+                                              "rhs2_rel_err: nbody_rhs on y1 against the oracle on the downloaded y1")
+            parity["tolerance"].update(state_rel_err=tol_state, rhs2_rel_err=tol_norm)
+            parity["ok"] = bool(parity["ok"] and extra["state_rel_err"] < tol_state
+                                and extra["rhs2_rel_err"] < tol_norm)
     # ---- secondary figure: the same workload with the uniform-mass specialisation OFF ----------
     # (the Plummer bodies have equal masses, which the library detects and factors out of the
     # pair sum; inputs with distinct masses -- the reference's own rand_bodies.txt -- take the
@@ -468,6 +503,72 @@ def run_b200(args):
         except capi.NBodyError as ex:
             det = {"error": str(ex)}
         secondary = dict(secondary or {}, deterministic=det)
+    # ---- the other BASELINE.json configs, short, after the timed region (secondary.configs) -----
+    # The headline line above is configs[3] FP64.  So that the driver's BENCH / SCALE records also
+    # hold the others, each gets a few device-timed steps here, with its own parity check against
+    # the oracle (owned rows of one RHS) -- same timing rules (warm-up >= 3, L2 flushed between
+    # steps, CUDA events on the library's stream, max over ranks), a fresh context each.
+    def other_config(precision, n_bodies, dist_name, steps, warmup, with_cpu=False):
+        sub = argparse.Namespace(**vars(args))
+        sub.n, sub.dist, sub.precision = n_bodies, dist_name, precision
+        sub.variant, sub.sym_variant, sub.pair_symmetry, sub.unimass, sub.deterministic = -1, -1, -1, -1, 0
+        bod, tau_s, eps_s = make_bodies(sub)
+        uid_s = None
+        if world > 1:
+            box = [capi.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            uid_s = box[0]
+        dt_s = np.float64 if precision == 64 else np.float32
+        try:
+            with capi.Context(n_bodies, precision, local, rank, world, uid_s) as c:
+                c.set_params(6.67e-11, eps_s)
+                c.upload_aos(np.ascontiguousarray(bod, dtype=dt_s))
+                for _ in range(warmup):
+                    c.step(scheme, tau_s, 1)
+                c.sync()
+                ms = []
+                for _ in range(steps):
+                    flush.zero_()
+                    torch.cuda.synchronize()
+                    barrier()
+                    c.step(scheme, tau_s, 1)
+                    c.sync()
+                    ms.append(max_over_ranks(c.timing().last_call_ms))
+                t = c.timing()
+                prow, pnorm, pper = parity_block(c, bod, eps_s, precision, rows_per_run=32, runs=2)
+            tol_norm, tol_row = PARITY_TOL[precision]
+            pn, pp = max_over_ranks(pnorm), max_over_ranks(pper)
+            val = stages * float(n_bodies) ** 2 * steps / (sum(ms) * 1e-3) / 1e9
+            shape = "Plummer sphere" if dist_name == "plummer" else "uniform-random cube"
+            out = {"workload": f"{shape} N={n_bodies} FP{precision} {args.scheme.upper()} tau={tau_s:g} "
+                               f"eps={eps_s:g} G=6.67e-11, L2 flushed between timed steps",
+                   "value": val, "unit": "G interactions/s", "n_gpus": world, "steps": steps,
+                   "warmup": warmup, "ms_per_step": float(np.mean(ms)),
+                   "dtype": "f64" if precision == 64 else "f32",
+                   "pair_symmetry": bool(t.pair_symmetry), "sym_variant": int(t.sym_variant),
+                   "uniform_mass_factored_out": bool(t.uniform_mass),
+                   "parity": {"rows": int(sum_over_ranks(float(prow))), "rhs_rel_err": pn,
+                              "per_row_max": pp, "ok": bool(pn < tol_norm and pp < tol_row)}}
+            if with_cpu and rank == 0:
+                # small enough for the reference's CPU code to evaluate a WHOLE RHS, not a row sample
+                rates, info = cpu_reference_sample(bod.astype(np.float64), eps_s, seconds=1e9, steps=2, warmup=1)
+                out["cpu_baseline"] = dict(info, value=float(np.mean(rates)),
+                                           whole_rhs=bool(f"rows [0,{n_bodies})" in info["sample"]))
+            return out
+        except capi.NBodyError as ex:
+            return {"error": str(ex)}
+
+    if not args.no_secondary and args.n == (1 << 20) and args.dist == "plummer" and args.precision == 64 \
+            and args.scheme == "rk4" and not args.p2p:
+        cfgs = {"plummer1m_fp32": dict(other_config(32, 1 << 20, "plummer", 3, 3),
+                                       baseline_config="configs[3], FP32 half"),
+                "plummer256k_fp64": dict(other_config(64, 1 << 18, "plummer", 5, 3),
+                                         baseline_config="configs[2] (strong scaling over --gpus)")}
+        if world == 1:
+            cfgs["uniform20k_fp64"] = dict(other_config(64, 20000, "uniform", 10, 3,
+                                                        with_cpu=not args.no_cpu_baseline),
+                                           baseline_config="configs[1] (1 GPU vs the lab_4 CPU path)")
+        secondary = dict(secondary or {}, configs=cfgs)
     total_launches = int(sum_over_ranks(float(launches)))
     sum_pairs = sum_over_ranks(float(pair_evals))
 

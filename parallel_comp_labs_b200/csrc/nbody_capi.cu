@@ -374,7 +374,13 @@ const SymVariant& sym_variant_pick(int prec, size_t n, int world, unsigned own_p
 	else pref = n_eff < 50000 ? p64_mid : (n_eff < 500000 || world > 1) ? p64_fine : p64_gen;
 	for (int k = 0; k < 3; ++k) {
 		const SymVariant& sv = tab[det ? twin[pref[k]] : pref[k]];
-		if (world == 1 || own_pad % (unsigned)(sv.threads * sv.ipt) == 0) return sv;
+		const unsigned rows = (unsigned)(sv.threads * sv.ipt);
+		// FP64, large n, only a 256-row build fits: entry 10 (64 threads, I = 4, j re-read) rather
+		// than the small-n entry 3 (I = 2) the lists end on -- measured on 2 GPUs at n = 1 100 000
+		// (per-rank block 2149 x 256): entry 10 3336 G int/s with equal masses, entry 3 2417 with
+		// general masses (profiles/r03_multi_2gpu.md)
+		if (world > 1 && rows == 256 && prec == 64 && n_eff >= 26000) break;
+		if (world == 1 || own_pad % rows == 0) return sv;
 	}
 	const int fits_all = prec == 64 ? 10 : 2;  // 256-row builds: divide every per-rank block
 	return tab[det ? twin[fits_all] : fits_all];
